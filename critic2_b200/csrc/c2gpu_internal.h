@@ -1,0 +1,36 @@
+// c2gpu_internal.h -- host-side declarations shared by the translation units of libc2gpu.so.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "promol_kernel.cuh"
+#include "wfn_kernel.cuh"
+
+namespace c2 {
+
+// Kernel configurations of the wavefunction kernel (TileCfg instantiations in wfn_launch.cu)
+struct WfnCfgInfo {
+  const char *name;
+  int wm, wn, ni, kc, ctas;   // template parameters
+  int P, NB, NT;
+  int ta, tb, tc;             // sub-tile shape of P points
+  size_t smem[3];             // dynamic shared memory for ND = 1, 4, 10
+};
+int wfn_num_configs();
+const WfnCfgInfo &wfn_cfg_info(int cfg);
+// cfg minimising the padded MO count (then the larger tile); `force` >= 0 overrides
+int wfn_choose_config(int nmo, int force);
+cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st);
+cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &xf, unsigned long long *count,
+                             cudaStream_t st);
+cudaError_t promol_launch(int nd, const PromolParams &p, int grid, cudaStream_t st);
+cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, double rhocut,
+                               double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
+                               double *raw_sums /*host[3]*/, long *ndat /*host*/, double *dat_dev, long maxdat,
+                               cudaStream_t st);
+
+extern long g_launches;       // kernels launched by the library
+
+}  // namespace c2

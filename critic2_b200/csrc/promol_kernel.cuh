@@ -1,0 +1,232 @@
+// promol_kernel.cuh -- promolecular density on a lattice: atom-binned radial-table sums.
+//
+// Replaces, per lattice, field%grd(type_promol) -> crystal%promolecular -> environ%promolecular
+// (src/fieldmod@proc.f90:802-808,834-840; src/environmod@proc.f90:1202-1327) with grid1%interp
+// (src/grid1mod@proc.f90:84-135) and the neighbour search list_near_atoms (src/environmod@proc.f90:895-1047).
+//
+// One CTA per tile of PT points (one thread per point).  The CTA walks the atom bins that can reach the tile's
+// bounding box, keeps (ordered warp-ballot compaction) the atoms whose species cutoff sphere touches the box in a
+// shared-memory list, and every thread sums its point's contributions from that list; the list is flushed in batches
+// so any number of candidates works.  Radial tables are stored node-interleaved (r,f,fp,fpp = one 32-byte sector per
+// node) with the six reciprocal node differences of each 4-node stencil precomputed on the host in the reference's
+// own arithmetic (x1dr12, :108-117).
+#pragma once
+#include "epilogue.cuh"
+
+namespace c2 {
+
+struct SpcDev {
+  int off, n;         // first node in the packed tables, ngrid (0: not initialised)
+  int z, pad;
+  double a, b;        // r_i = a*exp(b*(i-1)) log grid parameters (src/grid1mod.f90:30-31)
+  double rcut;        // min(cutrad(z), rmax) (:1246-1263); cutrad alone if the table is missing
+  double cutrad;
+  double rmax, r1;    // last and first node radius
+};
+
+struct PromolDev {
+  int nenv, ncell, nspc;
+  const double4 *atoms;     // nenv, sorted by bin: x, y, z, (species-1 | (cidx-1)<<8 ... packed as two ints)
+  const int *bin_start;     // nbx*nby*nbz + 1
+  double bin0[3], bin_inv;
+  int nbin[3];
+  const SpcDev *spc;
+  const double4 *nodes;     // packed (r, f, fp, fpp)
+  const double *inv;        // 8 doubles per stencil base: 1/(r1-r0),1/(r2-r0),1/(r2-r1),1/(r3-r0),1/(r3-r1),1/(r3-r2)
+  const unsigned char *fragmask;
+  double rcutmax;
+};
+
+struct PromolParams {
+  PromolDev m;
+  GridDesc g;
+  CellXf xf;
+  OutDesc o;
+  int nta, ntb, ntc;   // tile counts
+  double nci_const;
+  unsigned long long *count;   // optional: number of (point, atom) pairs inside the cutoffs
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void unpack_atom(const double4 &a, int &is, int &cidx) {
+  long long bits = __double_as_longlong(a.w);
+  is = (int)(bits & 0xffffffffll);
+  cidx = (int)(bits >> 32);
+}
+
+// grid1%interp (src/grid1mod@proc.f90:84-135) for r already clamped to >= r(1) by the caller (:1302)
+template <int ND>
+__device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &s, double r0, double &f, double &fp,
+                                              double &fpp) {
+  f = 0.0; fp = 0.0; fpp = 0.0;
+  if (r0 >= s.rmax) return;                                            // :98
+  int ir;
+  double r;
+  if (r0 <= s.r1) { ir = 1; r = s.r1; }                                // :103-105
+  else { ir = 1 + (int)floor(__ddiv_rn(log(__ddiv_rn(r0, s.a)), s.b)); r = r0; }   // :107
+  int base = min(max(ir, 2), s.n - 2) - 2;                             // :110, 0-based first node
+  const double4 *nd = m.nodes + s.off + base;
+  const double4 n0 = nd[0], n1 = nd[1], n2 = nd[2], n3 = nd[3];
+  const double4 *iv = reinterpret_cast<const double4 *>(m.inv + 8 * (size_t)(s.off + base));
+  const double4 ia = iv[0], ib = iv[1];
+  const double i10 = ia.x, i20 = ia.y, i21 = ia.z, i30 = ia.w, i31 = ib.x, i32 = ib.y;
+  const double d0 = r - n0.x, d1 = r - n1.x, d2 = r - n2.x, d3 = r - n3.x;
+  // prod_i = prod_{j != i} dr1(j) * x1dr12(i,j), j ascending (:119-126); x1dr12(i,j) = -x1dr12(j,i)
+  double p0 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d1, -i10), d2), -i20), d3), -i30);
+  double p1 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i10), d2), -i21), d3), -i31);
+  double p2 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i20), d1), i21), d3), -i32);
+  double p3 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i30), d1), i31), d2), i32);
+  f = n0.y * p0 + n1.y * p1 + n2.y * p2 + n3.y * p3;
+  if (ND > 1) fp = n0.z * p0 + n1.z * p1 + n2.z * p2 + n3.z * p3;
+  if (ND > 4) fpp = n0.w * p0 + n1.w * p1 + n2.w * p2 + n3.w * p3;
+}
+
+constexpr int PROMOL_PT = 256;    // points per tile = threads per CTA
+constexpr int PROMOL_CAP = 768;   // shared-memory atom list capacity (>= 2*PROMOL_PT)
+
+template <int ND>
+__global__ void __launch_bounds__(PROMOL_PT) promol_grid_kernel(const __grid_constant__ PromolParams p) {
+  constexpr int NT = PROMOL_PT, NW = NT / 32;
+  __shared__ double4 s_atom[PROMOL_CAP];
+  __shared__ int s_cnt[NW];
+  __shared__ double s_red[NW * 6];
+  __shared__ double s_bb[6];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const PromolDev &m = p.m;
+  const GridDesc &g = p.g;
+  const int na = grid_na(g), nb = grid_nb(g);
+  const int t = blockIdx.x;
+  const int ta0 = (t % p.nta) * g.ta, tb0 = ((t / p.nta) % p.ntb) * g.tb, tc0 = g.c0 + (g.c_part + (t / (p.nta * p.ntb)) * g.c_nparts) * g.tc;
+  const int a = ta0 + tid % g.ta, b = tb0 + (tid / g.ta) % g.tb, c = tc0 + tid / (g.ta * g.tb);
+  const bool valid = a < na && b < nb && c < g.c1;
+
+  double xc[3] = {0, 0, 0};
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  if (valid) {
+    double x[3], wc[3];
+    grid_point(g, a, b, c, x);
+    grd_wrap(p.xf, x, g.periodic, wc, xc);   // xc = wcr (:802)
+    center_cart(p.xf, xc, nullptr);          // :1242-1243
+#pragma unroll
+    for (int d = 0; d < 3; d++) { lo[d] = xc[d]; hi[d] = xc[d]; }
+  }
+  {
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        lo[d] = fmin(lo[d], __shfl_xor_sync(~0u, lo[d], o));
+        hi[d] = fmax(hi[d], __shfl_xor_sync(~0u, hi[d], o));
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int d = 0; d < 3; d++) { s_red[warp * 6 + d] = lo[d]; s_red[warp * 6 + 3 + d] = hi[d]; }
+    }
+    __syncthreads();
+    if (tid < 6) {
+      double v = s_red[tid];
+      for (int w = 1; w < NW; w++) v = (tid < 3) ? fmin(v, s_red[w * 6 + tid]) : fmax(v, s_red[w * 6 + tid]);
+      s_bb[tid] = v;
+    }
+    __syncthreads();
+  }
+  if (s_bb[0] > s_bb[3]) return;   // no valid point in this tile (block-uniform)
+
+  // bins that can reach the box
+  int blo[3], bhi[3];
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    blo[d] = max(0, (int)floor((s_bb[d] - m.rcutmax - m.bin0[d]) * m.bin_inv));
+    bhi[d] = min(m.nbin[d] - 1, (int)floor((s_bb[3 + d] + m.rcutmax - m.bin0[d]) * m.bin_inv));
+  }
+
+  double f = 0.0, gx = 0.0, gy = 0.0, gz = 0.0, hs[6] = {0, 0, 0, 0, 0, 0};
+  bool isnuc = false;
+  unsigned long long npair = 0;
+  int nlist = 0;
+
+  auto flush = [&]() {
+    __syncthreads();
+    if (valid) {
+      for (int i = 0; i < nlist; i++) {
+        const double4 at = s_atom[i];
+        int is, cidx;
+        unpack_atom(at, is, cidx);
+        const SpcDev s = m.spc[is];
+        // the reference takes at%r - x0 for the distance (:988) and xc - at%r for the gradient (:1308)
+        const double ex = at.x - xc[0], ey = at.y - xc[1], ez = at.z - xc[2];
+        const double d2 = ex * ex + ey * ey + ez * ez;
+        isnuc = isnuc || d2 < 1e-10;                                 // src/environmod@proc.f90:677
+        if (!within_cut(ex, ey, ez, d2, s.rcut, s.rcut * s.rcut)) continue;   // :998
+        if (s.n == 0) continue;                                      // :1298-1299
+        if (m.fragmask && !m.fragmask[cidx]) continue;               // :1287-1290
+        npair++;
+        double r = norm2_ref(ex, ey, ez);
+        if (r > s.cutrad) continue;                                  // :1295
+        r = fmax(fmax(r, s.r1), 1e-14);                              // :1302
+        double rho, rhop, rhopp;
+        radial_interp<ND>(m, s, r, rho, rhop, rhopp);
+        rho = fmax(rho, 0.0);                                        // :1304
+        f += rho;
+        if (ND > 1) {
+          const double xx = xc[0] - at.x, yy = xc[1] - at.y, zz = xc[2] - at.z;
+          const double rinv1 = 1.0 / r;
+          const double rinv1rp = rinv1 * rhop;
+          gx += xx * rinv1rp; gy += yy * rinv1rp; gz += zz * rinv1rp;   // :1309-1311
+          if (ND > 4) {
+            const double rfac = (rhopp - rinv1rp) * rinv1 * rinv1;      // :1314
+            hs[0] += rinv1rp + rfac * xx * xx;
+            hs[1] += rinv1rp + rfac * yy * yy;
+            hs[2] += rinv1rp + rfac * zz * zz;
+            hs[3] += rfac * xx * yy;
+            hs[4] += rfac * xx * zz;
+            hs[5] += rfac * yy * zz;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    nlist = 0;
+  };
+
+  for (int bz = blo[2]; bz <= bhi[2]; bz++)
+    for (int by = blo[1]; by <= bhi[1]; by++) {
+      const int rowbase = (bz * m.nbin[1] + by) * m.nbin[0];
+      const int i0 = m.bin_start[rowbase + blo[0]], i1 = m.bin_start[rowbase + bhi[0] + 1];
+      for (int base = i0; base < i1; base += NT) {
+        const int i = base + tid;
+        bool act = false;
+        double4 at;
+        if (i < i1) {
+          at = m.atoms[i];
+          int is, cidx;
+          unpack_atom(at, is, cidx);
+          const double rc = m.spc[is].rcut;
+          act = box_d2(s_bb, at.x, at.y, at.z) <= rc * rc * (1.0 + 1e-12) + 1e-9;
+        }
+        const unsigned mk = __ballot_sync(~0u, act);
+        if (lane == 0) s_cnt[warp] = __popc(mk);
+        __syncthreads();
+        int off = nlist, tot = 0;
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+          if (w < warp) off += s_cnt[w];
+          tot += s_cnt[w];
+        }
+        if (act) s_atom[off + __popc(mk & ((1u << lane) - 1u))] = at;
+        nlist += tot;
+        if (nlist > PROMOL_CAP - NT) flush(); else __syncthreads();
+      }
+    }
+  flush();
+  if (p.count) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) npair += __shfl_xor_sync(~0u, npair, o);
+    if (lane == 0 && npair) atomicAdd(p.count, npair);
+  }
+  if (valid) emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs, isnuc, p.nci_const);
+}
+#endif
+
+}  // namespace c2

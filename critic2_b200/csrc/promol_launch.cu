@@ -1,0 +1,171 @@
+// promol_launch.cu -- instantiations of the promolecular kernel and the NCIPLOT cutoff pass (sm_100a).
+#include "c2gpu_internal.h"
+
+namespace c2 {
+
+cudaError_t promol_launch(int nd, const PromolParams &p, int grid, cudaStream_t st) {
+  if (grid <= 0) return cudaSuccess;
+  if (nd == 1) promol_grid_kernel<1><<<grid, PROMOL_PT, 0, st>>>(p);
+  else if (nd == 4) promol_grid_kernel<4><<<grid, PROMOL_PT, 0, st>>>(p);
+  else promol_grid_kernel<10><<<grid, PROMOL_PT, 0, st>>>(p);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+// ---- NCIPLOT cutoff pass (src/nci@proc.f90:569-604, nfrag = 0) -----------------------------------------------------
+// HBM-bound streaming pass: 16-24 bytes read and up to 8 written per point.  Three kernels keep the reference's
+// loop order for the (rho, s) pair list and make the sums reproducible: (1) per-block pair counts and partial sums
+// (fixed-shape tree), (2) single-block exclusive scan of the counts + sequential sum of the partials,
+// (3) ordered pair emission (ballot compaction) and the cgrad = 100 masking.
+constexpr int CUT_NT = 256, CUT_PER = 8, CUT_BLK = CUT_NT * CUT_PER;
+
+struct CutArgs {
+  long npts;
+  const double *crho;
+  double *cgrad;
+  const double *rhoat;
+  double rhocut100, dimcut, rhoplot100, sr0, sr1, rho_void;
+  int onlyneg;
+};
+
+__device__ __forceinline__ void cut_point(const CutArgs &a, long i, bool &isdat, bool &mask, double &q, double &qp,
+                                          double &v, double &cr, double &cg) {
+  cr = a.crho[i];
+  cg = a.cgrad[i];
+  bool inter = true;
+  q = 0.0; qp = 0.0; v = 0.0;
+  if (a.rho_void > 0.0) {                                            // :573-582
+    double ra = a.rhoat[i];
+    inter = ra < a.rho_void;
+    if (inter) { q = fabs(cr) / 100.0; qp = ra; v = 1.0; }
+  }
+  isdat = fabs(cr) < a.rhocut100 && cg < a.dimcut && inter;          // :593
+  mask = fabs(cr) > a.rhoplot100 || !inter;                          // :596
+  mask = mask || cr < a.sr0 || cr > a.sr1;                           // :597
+  mask = mask || (cr > 0.0 && a.onlyneg);                            // :598
+}
+
+__global__ void __launch_bounds__(CUT_NT) cut_count_kernel(CutArgs a, unsigned *bcount, double *bsum) {
+  __shared__ double s_sum[3][CUT_NT / 32];
+  __shared__ unsigned s_c[CUT_NT / 32];
+  const long base = (long)blockIdx.x * CUT_BLK;
+  unsigned cnt = 0;
+  double q = 0, qp = 0, v = 0;
+  for (int k = 0; k < CUT_PER; k++) {
+    long i = base + (long)k * CUT_NT + threadIdx.x;
+    if (i < a.npts) {
+      bool isdat, mask;
+      double q1, qp1, v1, cr, cg;
+      cut_point(a, i, isdat, mask, q1, qp1, v1, cr, cg);
+      cnt += isdat;
+      q += q1; qp += qp1; v += v1;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(~0u, cnt, o);
+    q += __shfl_xor_sync(~0u, q, o);
+    qp += __shfl_xor_sync(~0u, qp, o);
+    v += __shfl_xor_sync(~0u, v, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { s_c[warp] = cnt; s_sum[0][warp] = q; s_sum[1][warp] = qp; s_sum[2][warp] = v; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned c = 0;
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int w = 0; w < CUT_NT / 32; w++) { c += s_c[w]; s0 += s_sum[0][w]; s1 += s_sum[1][w]; s2 += s_sum[2][w]; }
+    bcount[blockIdx.x] = c;
+    bsum[3 * (size_t)blockIdx.x] = s0; bsum[3 * (size_t)blockIdx.x + 1] = s1; bsum[3 * (size_t)blockIdx.x + 2] = s2;
+  }
+}
+
+// one block: exclusive scan of bcount -> boff (64-bit), totals -> out[0..3] = ndat, sumq, sumqp, sumv
+__global__ void __launch_bounds__(1024) cut_scan_kernel(int nblk, const unsigned *bcount, unsigned long long *boff,
+                                                        const double *bsum, double *out) {
+  __shared__ unsigned long long s_w[32];
+  __shared__ unsigned long long s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nblk; base += 1024) {
+    int i = base + threadIdx.x;
+    unsigned long long c = i < nblk ? bcount[i] : 0, incl = c;
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned long long t = __shfl_up_sync(~0u, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    unsigned long long off = s_carry;
+    for (int w = 0; w < warp; w++) off += s_w[w];
+    if (i < nblk) boff[i] = off + incl - c;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = off + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int i = 0; i < nblk; i++) { s0 += bsum[3 * (size_t)i]; s1 += bsum[3 * (size_t)i + 1]; s2 += bsum[3 * (size_t)i + 2]; }
+    out[0] = (double)s_carry; out[1] = s0; out[2] = s1; out[3] = s2;
+  }
+}
+
+__global__ void __launch_bounds__(CUT_NT) cut_emit_kernel(CutArgs a, const unsigned long long *boff, double *dat,
+                                                          long maxdat) {
+  __shared__ unsigned s_c[CUT_NT / 32];
+  const long base = (long)blockIdx.x * CUT_BLK;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long off = boff[blockIdx.x];
+  for (int k = 0; k < CUT_PER; k++) {
+    long i = base + (long)k * CUT_NT + threadIdx.x;
+    bool isdat = false, mask = false;
+    double q1, qp1, v1, cr = 0, cg = 0;
+    if (i < a.npts) cut_point(a, i, isdat, mask, q1, qp1, v1, cr, cg);
+    unsigned m = __ballot_sync(~0u, isdat);
+    if (lane == 0) s_c[warp] = __popc(m);
+    __syncthreads();
+    unsigned long long my = off;
+    unsigned tot = 0;
+    for (int w = 0; w < CUT_NT / 32; w++) {
+      if (w < warp) my += s_c[w];
+      tot += s_c[w];
+    }
+    my += __popc(m & ((1u << lane) - 1u));
+    if (isdat && dat && (long)my < maxdat) { dat[2 * my] = cr / 100.0; dat[2 * my + 1] = cg; }   // :594
+    if (mask && i < a.npts) a.cgrad[i] = 100.0;
+    off += tot;
+    __syncthreads();
+  }
+}
+
+cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, double rhocut,
+                               double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
+                               double *raw_sums, long *ndat, double *dat_dev, long maxdat, cudaStream_t st) {
+  raw_sums[0] = raw_sums[1] = raw_sums[2] = 0.0;
+  *ndat = 0;
+  if (npts <= 0) return cudaSuccess;
+  CutArgs a{npts, crho, cgrad, rhoat, rhocut * 100.0, dimcut, rhoplot * 100.0, sr0 * 100.0, sr1 * 100.0, rho_void, onlyneg};
+  int nblk = (int)((npts + CUT_BLK - 1) / CUT_BLK);
+  unsigned *bcount = nullptr;
+  unsigned long long *boff = nullptr;
+  double *bsum = nullptr, *out = nullptr;
+  cudaError_t e;
+  if ((e = cudaMalloc(&bcount, sizeof(unsigned) * nblk)) != cudaSuccess) return e;
+  if ((e = cudaMalloc(&boff, sizeof(unsigned long long) * nblk)) != cudaSuccess) return e;
+  if ((e = cudaMalloc(&bsum, sizeof(double) * 3 * nblk)) != cudaSuccess) return e;
+  if ((e = cudaMalloc(&out, sizeof(double) * 4)) != cudaSuccess) return e;
+  cut_count_kernel<<<nblk, CUT_NT, 0, st>>>(a, bcount, bsum);
+  cut_scan_kernel<<<1, 1024, 0, st>>>(nblk, bcount, boff, bsum, out);
+  cut_emit_kernel<<<nblk, CUT_NT, 0, st>>>(a, boff, dat_dev, maxdat);
+  g_launches += 3;
+  double h[4];
+  e = cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(bcount); cudaFree(boff); cudaFree(bsum); cudaFree(out);
+  if (e != cudaSuccess) return e;
+  *ndat = (long)h[0];
+  raw_sums[0] = h[1]; raw_sums[1] = h[2]; raw_sums[2] = h[3];
+  return cudaGetLastError();
+}
+
+}  // namespace c2

@@ -1,0 +1,134 @@
+// wfn_launch.cu -- instantiations and launch dispatch of the wavefunction grid kernel (sm_100a).
+#include "c2gpu_internal.h"
+
+namespace c2 {
+
+long g_launches = 0;
+
+// name, WM, WN, NI, KC, CTAS
+#define C2_WFN_CONFIGS(X) \
+  X(0, "S1", 8, 1, 1, 8, 2)   \
+  X(1, "S3", 8, 1, 3, 8, 1)   \
+  X(2, "M", 2, 4, 2, 16, 1)   \
+  X(3, "L", 2, 7, 2, 28, 1)   \
+  X(4, "L1", 1, 7, 2, 28, 2)
+
+static void tile_shape(int P, int &ta, int &tb, int &tc) {
+  switch (P) {
+    case 8: ta = 2; tb = 2; tc = 2; break;
+    case 16: ta = 4; tb = 2; tc = 2; break;
+    case 32: ta = 4; tb = 4; tc = 2; break;
+    default: ta = 4; tb = 4; tc = 4; break;
+  }
+}
+
+static std::vector<WfnCfgInfo> build_infos() {
+  std::vector<WfnCfgInfo> v;
+#define X(ID, NAME, WM, WN, NI, KC, CTAS)                                                            \
+  {                                                                                                  \
+    WfnCfgInfo i;                                                                                    \
+    i.name = NAME; i.wm = WM; i.wn = WN; i.ni = NI; i.kc = KC; i.ctas = CTAS;                        \
+    i.P = 8 * WM; i.NB = 8 * NI * WN; i.NT = 32 * WM * WN;                                           \
+    tile_shape(i.P, i.ta, i.tb, i.tc);                                                               \
+    i.smem[0] = TileCfg<1, WM, WN, NI, KC, CTAS>::SMEM;                                              \
+    i.smem[1] = TileCfg<4, WM, WN, NI, KC, CTAS>::SMEM;                                              \
+    i.smem[2] = TileCfg<10, WM, WN, NI, KC, CTAS>::SMEM;                                             \
+    v.push_back(i);                                                                                  \
+  }
+  C2_WFN_CONFIGS(X)
+#undef X
+  return v;
+}
+
+static const std::vector<WfnCfgInfo> &infos() {
+  static std::vector<WfnCfgInfo> v = build_infos();
+  return v;
+}
+int wfn_num_configs() { return (int)infos().size(); }
+const WfnCfgInfo &wfn_cfg_info(int cfg) { return infos()[cfg]; }
+
+int wfn_choose_config(int nmo, int force) {
+  if (force >= 0 && force < wfn_num_configs()) return force;
+  int nfrag = (nmo + 7) / 8;
+  if (nfrag <= 1) return 0;
+  if (nfrag <= 3) return 1;
+  int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
+  return (padM < padL) ? 2 : 3;
+}
+
+template <class C>
+static cudaError_t launch_one(const WfnParams &p, int grid, cudaStream_t st) {
+  static bool attr_set[16] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 16 && !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(wfn_grid_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  wfn_grid_kernel<C><<<grid, C::NT, C::SMEM, st>>>(p);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st) {
+#define X(ID, NAME, WM, WN, NI, KC, CTAS)                                          \
+  if (cfg == ID) {                                                                 \
+    if (nd == 1) return launch_one<TileCfg<1, WM, WN, NI, KC, CTAS>>(p, grid, st); \
+    if (nd == 4) return launch_one<TileCfg<4, WM, WN, NI, KC, CTAS>>(p, grid, st); \
+    return launch_one<TileCfg<10, WM, WN, NI, KC, CTAS>>(p, grid, st);             \
+  }
+  C2_WFN_CONFIGS(X)
+#undef X
+  return cudaErrorInvalidValue;
+}
+
+// ---- diagnostic: sum over points of n_act(p), the reference's own per-point primitive screen (:2747) ------------
+__global__ void __launch_bounds__(256) wfn_count_kernel(WfnDev w, GridDesc g, CellXf xf, unsigned long long *count) {
+  __shared__ double4 s_xa[256];
+  __shared__ double2 s_cut[256];
+  __shared__ int s_np[256];
+  const int na = grid_na(g), nb = grid_nb(g);
+  const size_t npl = (size_t)na * nb;
+  const size_t q = (size_t)blockIdx.x * 256 + threadIdx.x;
+  const size_t ntot = npl * (size_t)(g.c1 - g.c0);
+  const bool valid = q < ntot;
+  double wcr[3] = {0, 0, 0};
+  if (valid) {
+    int c = g.c0 + (int)(q / npl), b = (int)((q % npl) / na), a = (int)(q % na);
+    double x[3], wc[3];
+    grid_point(g, a, b, c, x);
+    grd_wrap(xf, x, g.periodic, wc, wcr);
+  }
+  unsigned long long n = 0;
+  for (int base = 0; base < w.nshell; base += 256) {
+    int s = base + threadIdx.x;
+    __syncthreads();
+    if (s < w.nshell) {
+      s_xa[threadIdx.x] = w.shell_xa[s];
+      s_cut[threadIdx.x] = w.shell_cut[s];
+      s_np[threadIdx.x] = w.shell_pbeg[s + 1] - w.shell_pbeg[s];
+    }
+    __syncthreads();
+    int m = min(256, w.nshell - base);
+    if (valid)
+      for (int i = 0; i < m; i++) {
+        double dx = wcr[0] - s_xa[i].x, dy = wcr[1] - s_xa[i].y, dz = wcr[2] - s_xa[i].z;
+        double d2 = dx * dx + dy * dy + dz * dz;
+        if (within_cut(dx, dy, dz, d2, s_cut[i].x, s_cut[i].y)) n += s_np[i];
+      }
+  }
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(~0u, n, o);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(count, n);
+}
+
+cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &xf, unsigned long long *count,
+                             cudaStream_t st) {
+  size_t ntot = (size_t)grid_na(g) * grid_nb(g) * (size_t)(g.c1 - g.c0);
+  if (ntot == 0) return cudaSuccess;
+  wfn_count_kernel<<<(unsigned)((ntot + 255) / 256), 256, 0, st>>>(w, g, xf, count);
+  g_launches++;
+  return cudaGetLastError();
+}
+
+}  // namespace c2

@@ -1,0 +1,292 @@
+"""ctypes binding of libc2gpu.so -- the host-side mirror of the Fortran ``gpu_interface`` module.
+
+Every call goes through the C ABI declared in include/c2gpu.h (the same symbols critic2's Fortran would bind with
+``bind(c)``).  There is no CPU fallback: if the shared library is missing or no B200 is visible, calls raise.
+
+Field objects mirror the reference's operator for this path, ``field%grd`` lifted to whole grids
+(/root/reference/src/fieldmod@proc.f90:613-842): ``WfnField`` = type_wfn, ``PromolField`` = type_promol.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libc2gpu.so")
+
+PROPS = ("f", "gx", "gy", "gz", "gmod", "hxx", "hxy", "hxz", "hyy", "hyz", "hzz", "lap")  # rhoplot@proc.f90:488-523
+RES_LEN = 16
+
+dp = C.POINTER(C.c_double)
+ip = C.POINTER(C.c_int)
+_lib = None
+
+
+class C2GpuError(RuntimeError):
+    pass
+
+
+class Unsupported(C2GpuError):
+    """status -1: the caller should keep its own CPU loop."""
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise C2GpuError(f"{LIB_PATH} is missing: build it with `make -C critic2_b200/csrc` "
+                             "(python __graft_entry__.py build); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.c2gpu_init.argtypes = [C.c_int, ip]
+        L.c2gpu_init_devices.argtypes = [ip, C.c_int]
+        L.c2gpu_last_error.argtypes = [C.c_char_p, C.c_int]
+        L.c2gpu_launch_count.restype = C.c_long
+        L.c2gpu_set_option.argtypes = [C.c_char_p, C.c_int]
+        L.c2gpu_destroy.argtypes = [C.c_void_p]
+        L.c2gpu_wfn_create.argtypes = [C.c_int, dp, C.c_int, ip, ip, dp, dp, C.c_int, C.c_int, dp, dp, C.c_int, C.c_int,
+                                       C.c_int, ip, ip, dp, dp, dp, C.c_int, dp, dp, C.POINTER(C.c_void_p)]
+        L.c2gpu_promol_create.argtypes = [C.c_int, C.c_int, dp, ip, ip, C.c_int, ip, ip, dp, dp, dp, dp, dp, dp, dp,
+                                          C.c_int, dp, dp, dp, dp, C.c_char_p, C.POINTER(C.c_void_p)]
+        L.c2gpu_eval_grid.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint, C.POINTER(dp)]
+        L.c2gpu_eval_grid_dev.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p),
+                                          C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_nci_grid.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, dp, dp, dp]
+        L.c2gpu_nci_grid_dev.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_nci_cutoffs.argtypes = [C.c_long, dp, dp, dp, C.c_double, C.c_double, C.c_double, dp, C.c_int,
+                                        C.c_double, C.c_double, dp, C.POINTER(C.c_long), dp, C.c_long]
+        L.c2gpu_nci_cutoffs_dev.argtypes = [C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
+                                            C.c_double, dp, C.c_int, C.c_double, dp, C.POINTER(C.c_long), C.c_void_p,
+                                            C.c_long, C.c_void_p]
+        L.c2gpu_promol_grid.argtypes = [C.c_void_p, ip, dp]
+        L.c2gpu_promol_grid_dev.argtypes = [C.c_void_p, ip, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_eval_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp]
+        L.c2gpu_wfn_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_int, dp]
+        L.c2gpu_promol_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, dp]
+        L.c2gpu_wfn_config.argtypes = [C.c_void_p, ip]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc == 0:
+        return
+    buf = C.create_string_buffer(512)
+    lib().c2gpu_last_error(buf, 512)
+    msg = buf.value.decode(errors="replace")
+    if rc == -1:
+        raise Unsupported(msg)
+    raise C2GpuError(f"c2gpu status {rc}: {msg}")
+
+
+def _d(a):
+    return a.ctypes.data_as(dp)
+
+
+def _i(a):
+    return a.ctypes.data_as(ip)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _colmajor(m):
+    return np.ascontiguousarray(np.asarray(m, float).T).reshape(-1)
+
+
+def init(ndev: int = 0) -> int:
+    n = C.c_int(0)
+    _check(lib().c2gpu_init(ndev, C.byref(n)))
+    return n.value
+
+
+def init_devices(devs) -> None:
+    a = _i32(list(devs))
+    _check(lib().c2gpu_init_devices(_i(a), len(a)))
+
+
+def set_option(name: str, value: int) -> None:
+    _check(lib().c2gpu_set_option(name.encode(), int(value)))
+
+
+def launch_count() -> int:
+    return int(lib().c2gpu_launch_count())
+
+
+def _grid_args(x0, xd, nn):
+    return _f64(x0), _colmajor(xd), _i32(nn)
+
+
+class _Field:
+    """Common grid drivers of a field handle."""
+
+    handle = None
+
+    def close(self):
+        if self.handle is not None and _lib is not None:
+            _lib.c2gpu_destroy(self.handle)
+        self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- rhoplot_cube evaluation loop, rhoplot@proc.f90:582-631 -------------------------------------------------
+    def cube(self, x0, xd, nn, props=PROPS, nder: int = 2, periodic: bool = False):
+        """HOST arrays through the C ABI (copies inside). xd[:, i] is the i-th step vector.
+        Returns {prop: array (nn3, nn2, nn1)} = lf(ix,iy,iz) with x fastest."""
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        names = [p for p in PROPS if p in props]
+        mask = sum(1 << PROPS.index(p) for p in names)
+        npt = int(nna[0]) * int(nna[1]) * int(nna[2])
+        outs = [np.empty(npt) for _ in names]
+        arr = (dp * len(outs))(*[_d(o) for o in outs])
+        _check(lib().c2gpu_eval_grid(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, arr))
+        return {p: o.reshape(nna[2], nna[1], nna[0]) for p, o in zip(names, outs)}
+
+    def cube_dev(self, x0, xd, nn, outs, props, nder: int = 2, periodic: bool = False, iz0: int = 0, iz1=None,
+                 stream: int = 0):
+        """DEVICE arrays (torch CUDA float64 tensors of nn1*nn2*nn3 elements, one per property in PROPS order)."""
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        names = [p for p in PROPS if p in props]
+        mask = sum(1 << PROPS.index(p) for p in names)
+        assert len(outs) == len(names)
+        ptrs = (C.c_void_p * len(outs))(*[C.c_void_p(t.data_ptr()) for t in outs])
+        _check(lib().c2gpu_eval_grid_dev(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs,
+                                         iz0, int(nna[2]) if iz1 is None else iz1, C.c_void_p(stream)))
+
+    # -- nciplot evaluation loop, nci@proc.f90:499-561 ----------------------------------------------------------
+    def nci(self, x0, xmat, nstep, promol: "_Field | None" = None):
+        """Returns crho, cgrad[, rhoat] as (n1, n2, n3) arrays, z fastest (the reference's crho(k,j,i))."""
+        x0a, xda, nna = _grid_args(x0, xmat, nstep)
+        npt = int(nna[0]) * int(nna[1]) * int(nna[2])
+        crho, cgrad = np.empty(npt), np.empty(npt)
+        rhoat = np.empty(npt) if promol is not None else None
+        _check(lib().c2gpu_nci_grid(self.handle, promol.handle if promol is not None else None, _d(x0a), _d(xda),
+                                    _i(nna), _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None))
+        shp = (nna[0], nna[1], nna[2])
+        return crho.reshape(shp), cgrad.reshape(shp), (rhoat.reshape(shp) if rhoat is not None else None)
+
+    def nci_dev(self, x0, xmat, nstep, crho, cgrad, rhoat=None, promol: "_Field | None" = None, i0: int = 0, i1=None,
+                stream: int = 0):
+        x0a, xda, nna = _grid_args(x0, xmat, nstep)
+        _check(lib().c2gpu_nci_grid_dev(self.handle, promol.handle if promol is not None else None, _d(x0a), _d(xda),
+                                        _i(nna), C.c_void_p(crho.data_ptr()), C.c_void_p(cgrad.data_ptr()),
+                                        C.c_void_p(rhoat.data_ptr()) if rhoat is not None else None, i0,
+                                        int(nna[0]) if i1 is None else i1, C.c_void_p(stream)))
+
+    # -- field%grd on a point list, fieldmod@proc.f90:613-842 ---------------------------------------------------
+    def points(self, pts, nder: int = 2, periodic: bool = True):
+        pts = _f64(pts).reshape(-1, 3)
+        res = np.empty((pts.shape[0], RES_LEN))
+        _check(lib().c2gpu_eval_points(self.handle, pts.shape[0], _d(pts), nder, int(periodic), _d(res)))
+        return res
+
+
+class WfnField(_Field):
+    """type_wfn field: the flat molwfn arrays (critic2_b200.wfn.Molwfn) placed in a molecular cell
+    (critic2_b200.structure.Structure); wfn_private.f90:83-131."""
+
+    def __init__(self, f, st):
+        if f.dran is None:
+            from .wfn import complete_struct
+            complete_struct(f)
+        self.f, self.st = f, st
+        h = C.c_void_p()
+        ne = f.nedf
+        nmoall = f.cmo.shape[1]
+        _check(lib().c2gpu_wfn_create(
+            f.natom, _d(_f64(st.r)), f.npri, _i(_i32(f.icenter)), _i(_i32(f.itype)), _d(_f64(f.e)), _d(_f64(f.dran)),
+            f.nmoocc, nmoall, _d(_f64(f.cmo)), _d(_f64(f.occ)), f.wfntyp, f.nalpha, ne,
+            _i(_i32(f.icenter_edf)) if ne else None, _i(_i32(f.itype_edf)) if ne else None,
+            _d(_f64(f.e_edf)) if ne else None, _d(_f64(f.c_edf)) if ne else None,
+            _d(_f64(f.dran_edf)) if ne else None, int(st.ismolecule), _d(_colmajor(st.m_x2c)), _d(_colmajor(st.m_c2x)),
+            C.byref(h)))
+        self.handle = h
+
+    def config(self):
+        a = np.zeros(8, np.int32)
+        _check(lib().c2gpu_wfn_config(self.handle, _i(a)))
+        return dict(cfg=int(a[0]), points_per_tile=int(a[1]), mo_block=int(a[2]), nblk=int(a[3]), threads=int(a[4]),
+                    kchunk=int(a[5]), nshell=int(a[6]), grid=int(a[7]))
+
+    def count_active(self, x0, xd, nn, periodic: bool = False, iz0: int = 0, iz1=None) -> float:
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        s = C.c_double(0)
+        _check(lib().c2gpu_wfn_count_active(self.handle, _d(x0a), _d(xda), _i(nna), int(periodic), iz0,
+                                            int(nna[2]) if iz1 is None else iz1, C.byref(s)))
+        return s.value
+
+
+class PromolField(_Field):
+    """type_promol field: environment atoms + radial tables. tables: {Z: dict(a,b,r,f,fp,fpp)}."""
+
+    def __init__(self, st, tables, fragmask=None):
+        from .structure import CUTRAD
+        self.st = st
+        zspc, iss = st.species()
+        r_env, cidx = st.environment_atoms()
+        ispc = iss[cidx - 1]
+        ngrid, aa, bb, cut = [], [], [], []
+        tr, tf, tfp, tfpp = [], [], [], []
+        for z in zspc:
+            t = tables.get(int(z))
+            cut.append(float(CUTRAD[int(z) - 1]))
+            if t is None:
+                ngrid.append(0); aa.append(0.0); bb.append(1.0)
+                continue
+            ngrid.append(len(t["r"])); aa.append(float(t["a"])); bb.append(float(t["b"]))
+            tr.append(_f64(t["r"])); tf.append(_f64(t["f"])); tfp.append(_f64(t["fp"])); tfpp.append(_f64(t["fpp"]))
+        cat = lambda x: np.concatenate(x) if x else np.zeros(1)
+        h = C.c_void_p()
+        frag = None if fragmask is None else np.ascontiguousarray(fragmask, np.uint8).tobytes()
+        _check(lib().c2gpu_promol_create(
+            r_env.shape[0], st.ncell, _d(_f64(r_env)), _i(_i32(ispc)), _i(_i32(cidx)), len(zspc), _i(_i32(zspc)),
+            _i(_i32(ngrid)), _d(_f64(aa)), _d(_f64(bb)), _d(_f64(cut)), _d(cat(tr)), _d(cat(tf)), _d(cat(tfp)),
+            _d(cat(tfpp)), int(st.ismolecule), _d(_colmajor(st.m_x2c)), _d(_colmajor(st.m_c2x)),
+            _d(_colmajor(st.m_xr2c)), _d(_colmajor(st.m_c2xr)), frag, C.byref(h)))
+        self.handle = h
+        self.nenv = int(r_env.shape[0])
+
+    # -- crystal%promolecular_grid, crystalmod@proc.f90:5118-5158 ------------------------------------------------
+    def promolecular_grid(self, n):
+        na = _i32(n)
+        out = np.empty(int(na[0]) * int(na[1]) * int(na[2]))
+        _check(lib().c2gpu_promol_grid(self.handle, _i(na), _d(out)))
+        return out.reshape(na[2], na[1], na[0])
+
+    def promolecular_grid_dev(self, n, out, iz0: int = 0, iz1=None, stream: int = 0):
+        na = _i32(n)
+        _check(lib().c2gpu_promol_grid_dev(self.handle, _i(na), C.c_void_p(out.data_ptr()), iz0,
+                                           int(na[2]) if iz1 is None else iz1, C.c_void_p(stream)))
+
+    def count_active(self, x0, xd, nn, periodic: bool = False) -> float:
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        s = C.c_double(0)
+        _check(lib().c2gpu_promol_count_active(self.handle, _d(x0a), _d(xda), _i(nna), int(periodic), C.byref(s)))
+        return s.value
+
+
+def nci_cutoffs(crho, cgrad, rhoat=None, rhocut=0.2, dimcut=2.0, rhoplot=0.1, srhorange=(-1e30, 1e30), onlyneg=False,
+                rho_void=-1.0, omega=1.0, want_dat=True):
+    """nciplot cutoff pass (nci@proc.f90:569-604) on HOST arrays; cgrad is modified in place.
+    Returns (sums[3], dat (ndat, 2))."""
+    npts = crho.size
+    sums = np.zeros(3)
+    nd = C.c_long(0)
+    dat = np.zeros((npts if want_dat else 0, 2))
+    sr = _f64(srhorange)
+    assert crho.flags.c_contiguous and cgrad.flags.c_contiguous
+    _check(lib().c2gpu_nci_cutoffs(npts, _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None, rhocut, dimcut,
+                                   rhoplot, _d(sr), int(onlyneg), rho_void, omega, _d(sums), C.byref(nd),
+                                   _d(dat) if want_dat else None, npts if want_dat else 0))
+    return sums, dat[:nd.value].copy(), nd.value

@@ -1,0 +1,129 @@
+/*
+ * c2gpu.h -- C ABI of the B200 (sm_100a) grid field-evaluation module for critic2.
+ *
+ * This is the drop-in boundary: the entry points a Fortran `interface ... bind(c)` block in critic2 binds
+ * (fortran/gpu_interface.f90 shows the binding; INTEGRATION.md the call-site patches).  The reference has no FFI for
+ * this path, so the boundary is lifted to the grid loops that call field%grd point by point; each entry cites the
+ * reference loop or routine it replaces.  All citations are relative to /root/reference/.
+ *
+ * Conventions
+ *   - every function returns int: 0 ok, -1 "unsupported input" (caller falls through to its own CPU loop),
+ *     >0 error (message via c2gpu_last_error).  Nothing aborts or throws across the ABI
+ *     (reference error convention: ferror, src/tools_io@proc.F90:1233).
+ *   - all coordinates are Cartesian bohr in the cell frame; 3x3 matrices are column-major (Fortran order);
+ *     atom / primitive ids are 1-based like the reference.
+ *   - the caller owns every host array; *_create copies its inputs to every selected device.
+ *   - *_dev variants take DEVICE pointers (on the handle's first device) and a cudaStream_t passed as void*;
+ *     they are what a one-process-per-GPU host (bench.py under torchrun) uses.  The plain variants take HOST
+ *     pointers, spread the slowest grid index over all devices of the handle and copy the result back.
+ *   - there is no CPU fallback inside this library.
+ */
+#ifndef C2GPU_H
+#define C2GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library / device management ---------------------------------------------------------------------------- */
+/* Select devices 0..min(ndev_req,visible)-1 (ndev_req<=0: all visible).  *ndev = number selected. */
+int c2gpu_init(int ndev_req, int *ndev);
+/* Select an explicit device list (one-process-per-GPU hosts pass their LOCAL_RANK). */
+int c2gpu_init_devices(const int *devs, int n);
+int c2gpu_finalize(void);
+/* Copy the last error message (NUL terminated) into buf. */
+int c2gpu_last_error(char *buf, int len);
+/* Number of kernels launched by this library since load (the bench's gpu_launches claim). */
+long c2gpu_launch_count(void);
+
+/* ---- field handles ------------------------------------------------------------------------------------------ */
+/*
+ * Wavefunction field = the flat image of type molwfn after read_* + prune_primitives + complete_struct
+ * (src/wfn_private.f90:83-131; tables from src/wfn_private@proc.F90:3077-3184).  Replaces the data side of
+ * molwfn%rho2 (src/wfn_private@proc.F90:2032-2228) and calculate_mo_gto (:2673-2781) / calculate_edf (:2783-2873).
+ *   xyz        3*natom   env%at(i)%r (cell frame)
+ *   icenter    npri      1-based atom of each primitive;  itype npri  primitive type 1..56 (:2695-2705)
+ *   expo,dran  npri      exponent and screening radius sqrt(-ln(1e-12)/expo) (:3102-3106)
+ *   cmo        column-major ldc x npri (ldc = nmoall >= nmoocc), MO index fastest: cmo(imo,ipri)
+ *   occ        nmoocc;   wfntyp 0 rhf, 1 uhf, 2 frac (src/wfn_private.f90:142-144); nalpha: # alpha MOs (uhf)
+ *   EDF arrays (nedf may be 0) as read_wfx :864-873; dran_edf like dran.
+ *   cell: ismolecule and the matrices field%grd uses to wrap the point (src/fieldmod@proc.f90:698-721).
+ *         Only ismolecule != 0 is supported for wavefunction fields (returns -1 otherwise).
+ */
+int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter, const int *itype,
+                     const double *expo, const double *dran, int nmoocc, int ldc, const double *cmo,
+                     const double *occ, int wfntyp, int nalpha, int nedf, const int *icenter_edf,
+                     const int *itype_edf, const double *e_edf, const double *c_edf, const double *dran_edf,
+                     int ismolecule, const double *m_x2c, const double *m_c2x, void **handle);
+
+/*
+ * Promolecular field = environ atoms (cell atoms + periodic images, src/environmod@proc.f90:139-213) + the
+ * radial tables agrid(:) (src/grid1mod.f90:25-46).  Replaces environ%promolecular (src/environmod@proc.f90:1202-1327)
+ * with grid1%interp (src/grid1mod@proc.f90:84-135).
+ *   xyz_env 3*nenv Cartesian (main reduced cell + images); ispc nenv 1-based species; cidx nenv 1-based cell atom
+ *   per species: zspc, ngrid, a, b, cutrad (src/global.f90:51-93); tables packed one species after another
+ *   (offset of species s = sum ngrid[0..s-1]): tab_r, tab_f, tab_fp, tab_fpp.  ngrid[s] = 0: table not initialised.
+ *   m_* : cell and reduced-cell matrices (grd wrap :698-721; y2z_center src/environmod@proc.f90:426-444)
+ *   fragmask: NULL or ncell flags (type_promol_frag, :1287-1290)
+ */
+int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *ispc, const int *cidx, int nspc,
+                        const int *zspc, const int *ngrid, const double *a, const double *b, const double *cutrad,
+                        const double *tab_r, const double *tab_f, const double *tab_fp, const double *tab_fpp,
+                        int ismolecule, const double *m_x2c, const double *m_c2x, const double *m_xr2c,
+                        const double *m_c2xr, const unsigned char *fragmask, void **handle);
+int c2gpu_destroy(void *handle);
+
+/* ---- CUBE: rhoplot_cube evaluation loop, src/rhoplot@proc.f90:582-631 ---------------------------------------- */
+/* property bits of outmask = nti of :488-523: 0 f, 1 gx, 2 gy, 3 gz, 4 gmod, 5 hxx, 6 hxy, 7 hxz, 8 hyy, 9 hyz,
+   10 hzz, 11 lap.  out[] holds one nn1*nn2*nn3 array per set bit (ascending bit order), x fastest (lf(ix,iy,iz)).
+   xd: column-major step vectors.  nder is 2 in the reference's loop (:595); 0/1 are accepted (grd semantics). */
+#define C2GPU_NPROP 12
+int c2gpu_eval_grid(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
+                    unsigned outmask, double *const *out);
+/* slab [iz0,iz1) of the same loop into full-size DEVICE arrays */
+int c2gpu_eval_grid_dev(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
+                        unsigned outmask, double *const *out_dev, int iz0, int iz1, void *stream);
+
+/* ---- NCIPLOT: evaluation loop src/nci@proc.f90:499-561, cutoff pass :569-604 ---------------------------------- */
+/* crho/cgrad/rhoat are (0:n3-1,0:n2-1,0:n1-1): z fastest, x slowest (:458-469).  hpromol/rhoat may be NULL. */
+int c2gpu_nci_grid(void *href, void *hpromol, const double x0[3], const double xmat[9], const int nstep[3],
+                   double *crho, double *cgrad, double *rhoat);
+/* slab [i0,i1) of the slowest (x) index into full-size DEVICE arrays */
+int c2gpu_nci_grid_dev(void *href, void *hpromol, const double x0[3], const double xmat[9], const int nstep[3],
+                       double *crho_dev, double *cgrad_dev, double *rhoat_dev, int i0, int i1, void *stream);
+/* Cutoff pass (nfrag = 0).  Modifies cgrad in place; sums[3] = sumq,sumqp,sumv (scaled by omega/N, :600-603);
+   *ndat = number of (rho,s) pairs of the .dat file; dat (2*maxdat doubles, may be NULL) receives the first maxdat
+   pairs in the reference's loop order.  rho_void <= 0 disables the VOID test (rhoat may then be NULL). */
+int c2gpu_nci_cutoffs(long npts, double *crho, double *cgrad, const double *rhoat, double rhocut, double dimcut,
+                      double rhoplot, const double srhorange[2], int onlyneg, double rho_void, double omega,
+                      double sums[3], long *ndat, double *dat, long maxdat);
+int c2gpu_nci_cutoffs_dev(long npts, const double *crho_dev, double *cgrad_dev, const double *rhoat_dev,
+                          double rhocut, double dimcut, double rhoplot, const double srhorange[2], int onlyneg,
+                          double rho_void, double raw_sums[3], long *ndat, double *dat_dev, long maxdat,
+                          void *stream);
+
+/* ---- whole-cell promolecular grid: crystal%promolecular_grid, src/crystalmod@proc.f90:5118-5158 --------------- */
+int c2gpu_promol_grid(void *hpromol, const int n[3], double *out);
+int c2gpu_promol_grid_dev(void *hpromol, const int n[3], double *out_dev, int iz0, int iz1, void *stream);
+
+/* ---- arbitrary point lists: field%grd, src/fieldmod@proc.f90:613-842 ("next" row: mesh%fill, planes, lines) ---- */
+/* res: npts x C2GPU_RES_LEN doubles: [0] f, [1..3] gf, [4..12] hf (column-major), [13] gfmod, [14] del2f, [15] isnuc */
+#define C2GPU_RES_LEN 16
+int c2gpu_eval_points(void *h, long npts, const double *pts, int nder, int periodic, double *res);
+
+/* ---- diagnostics used by the roofline accounting -------------------------------------------- */
+/* Sum over the grid slab of n_act(p) = #{primitives with dist <= dran} (the reference's own screen, :2747). */
+int c2gpu_wfn_count_active(void *h, const double x0[3], const double xd[9], const int nn[3], int periodic, int iz0,
+                           int iz1, double *sum_nact);
+/* Sum over the grid of the number of atoms inside the promolecular cutoffs (src/environmod@proc.f90:1284-1300). */
+int c2gpu_promol_count_active(void *h, const double x0[3], const double xd[9], const int nn[3], int periodic,
+                              double *sum_nat);
+/* Kernel configuration chosen for a wavefunction handle: points per tile, MO columns per block, blocks, threads. */
+int c2gpu_wfn_config(void *h, int cfg[8]);
+/* Override tunables (name/value); used by bench sweeps.  Unknown names return 1. */
+int c2gpu_set_option(const char *name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
