@@ -1,0 +1,121 @@
+"""Host-side mirror of the two task drivers whose evaluation loops the CUDA module replaces.
+
+* ``cube_grid`` / ``rhoplot_cube`` -- CUBE: grid definition and property selection of
+  /root/reference/src/rhoplot@proc.f90:381-447, 536-544 (end point excluded), evaluation loop :582-631.
+* ``nci_grid`` / ``nciplot``       -- NCIPLOT: box, step and defaults of /root/reference/src/nci@proc.f90:119-162,
+  350-410; evaluation loop :499-561; cutoff pass :569-604.
+
+Only bookkeeping lives here; all field arithmetic is in csrc/ behind the C ABI (critic2_b200.gpu).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import gpu
+from .structure import Structure
+
+
+def cube_grid(st: Structure, nn, x0=None, x1=None, cell: bool = True):
+    """CUBE CELL nx ny nz (cell=True) or CUBE x0 x1 nx ny nz.  Returns (x0 (3,), xd (3,3) with xd[:,i] the i-th step
+    vector, nn): rhoplot@proc.f90:412-426, 542-544.  For molecules x0/x1 are real-space Cartesian (bohr) and are
+    shifted by molx0 like :401-404."""
+    nn = np.maximum(np.asarray(nn, np.int32), 2)
+    if cell:
+        xd = np.eye(3)
+        o = np.zeros(3)
+    else:
+        x0 = np.asarray(x0, float)
+        x1 = np.asarray(x1, float)
+        if st.ismolecule:
+            x0 = st.m_c2x @ (x0 - st.molx0)
+            x1 = st.m_c2x @ (x1 - st.molx0)
+        xd = np.diag(x1 - x0)
+        o = x0
+    o = st.m_x2c @ o
+    xd = st.m_x2c @ xd
+    xd = xd / nn.astype(float)[None, :]
+    return o, xd, nn
+
+
+def rhoplot_cube(field: "gpu._Field", st: Structure, nn, props=("f",), x0=None, x1=None, cell: bool = True):
+    """Evaluate the CUBE properties on the grid; one nder=2 evaluation serves every requested property
+    (the reference re-runs the whole loop per CUBE command, :595)."""
+    o, xd, nn = cube_grid(st, nn, x0, x1, cell)
+    return field.cube(o, xd, nn, props=props, nder=2, periodic=not st.ismolecule), (o, xd, nn)
+
+
+@dataclass
+class NciOptions:
+    """Defaults of nci@proc.f90:137-162."""
+    rhocut: float = 0.2
+    dimcut: float = 2.0
+    rhoplot: float = 0.1
+    dimplot: float = 0.5
+    isden: bool = True            # reference field is a density (not promolecular): :119,137-153
+    srhorange: tuple = (-1e30, 1e30)
+    onlyneg: bool = False
+    rho_void: float = -1.0
+    xinc: float = 0.1
+
+    @staticmethod
+    def promolecular():
+        return NciOptions(rhocut=0.2, dimcut=1.0, rhoplot=0.12, dimplot=0.3, isden=False)
+
+
+def nci_grid(st: Structure, nstep=None, xinc: float = 0.1, rthres: float | None = None):
+    """NCIPLOT box and step (no fragments): nci@proc.f90:122-134, 350-410.  Returns (x0, xmat, nstep)."""
+    if st.ismolecule:
+        x0 = st.m_x2c @ st.molborder
+        x1 = st.m_x2c @ (1.0 - st.molborder)
+        periodic = False
+    else:
+        x0 = st.m_x2c @ np.zeros(3)
+        x1 = st.m_x2c @ np.ones(3)
+        periodic = True
+    if rthres is not None:
+        x0 = x0 - rthres
+        x1 = x1 + rthres
+    x0 = st.m_c2x @ x0
+    x1 = st.m_c2x @ x1
+    xmat = np.zeros((3, 3))
+    if periodic:
+        ns = np.zeros(3, np.int32)
+        for i in range(3):
+            e = np.zeros(3)
+            e[i] = 1.0
+            v = st.m_x2c @ e
+            ns[i] = int(nstep[i]) if nstep is not None else math.ceil(np.linalg.norm(v) / xinc)
+            xmat[:, i] = v / float(ns[i])
+        x0c = st.m_x2c @ x0
+    else:
+        a = st.m_x2c @ x0
+        b = st.m_x2c @ x1
+        x0c, x1c = np.minimum(a, b), np.maximum(a, b)
+        if nstep is None:
+            ns = np.ceil(np.abs(x1c - x0c) / xinc).astype(np.int32)
+            inc = np.full(3, xinc)
+        else:
+            ns = np.asarray(nstep, np.int32)
+            inc = (x1c - x0c) / ns.astype(float)
+        for i in range(3):
+            xmat[i, i] = inc[i]
+    return x0c, xmat, ns
+
+
+def nciplot(field: "gpu._Field", st: Structure, nstep=None, opts: NciOptions | None = None,
+            promol: "gpu._Field | None" = None, rthres: float | None = None):
+    """NCIPLOT evaluation + cutoff pass.  Returns dict(crho, cgrad, rhoat, sums, dat, ndat, grid)."""
+    opts = opts or NciOptions()
+    x0, xmat, ns = nci_grid(st, nstep, opts.xinc, rthres)
+    use_promol = promol if opts.rho_void > 0 else None
+    crho, cgrad, rhoat = field.nci(x0, xmat, ns, promol=use_promol)
+    cg = cgrad.reshape(-1).copy()
+    sums, dat, ndat = gpu.nci_cutoffs(crho.reshape(-1), cg, None if rhoat is None else rhoat.reshape(-1),
+                                      rhocut=opts.rhocut, dimcut=opts.dimcut, rhoplot=opts.rhoplot,
+                                      srhorange=opts.srhorange, onlyneg=opts.onlyneg, rho_void=opts.rho_void,
+                                      omega=st.omega)
+    return dict(crho=crho, cgrad=cgrad, cgrad_masked=cg.reshape(cgrad.shape), rhoat=rhoat, sums=sums, dat=dat,
+                ndat=ndat, grid=(x0, xmat, ns))

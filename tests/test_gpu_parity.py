@@ -1,0 +1,228 @@
+"""GPU parity tests: the CUDA path called through the C ABI (host buffers) against the CPU oracle on the same inputs.
+
+Tolerances (BASELINE.json north_star): rho <= 1e-10 relative, derivatives and RDG <= 1e-8, identical NCI
+classification (points with |lambda2| below the eigen-solver's own resolution are counted and excluded).
+"""
+import numpy as np
+import pytest
+
+import cases
+from cases import check_rho, check_vec
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def G():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from critic2_b200 import gpu
+    gpu.init_devices([0])
+    return gpu
+
+
+@pytest.fixture(scope="module")
+def O():
+    import oracle
+    oracle.build()
+    return oracle
+
+
+def _ofield(O, f, st):
+    env = O.Environ(st)
+    return O.Field(env, wfn=O.Wfn(f))
+
+
+def _compare_cube(got, ref):
+    e = {"rho": check_rho(got["f"], ref["f"])}
+    g = np.stack([got[k] for k in ("gx", "gy", "gz")], -1)
+    gr = np.stack([ref[k] for k in ("gx", "gy", "gz")], -1)
+    e["grad"] = check_vec(g, gr, "grad", rho=ref["f"])
+    hk = ("hxx", "hxy", "hxz", "hyy", "hyz", "hzz")
+    e["hess"] = check_vec(np.stack([got[k] for k in hk], -1), np.stack([ref[k] for k in hk], -1), "hessian", rho=ref["f"])
+    e["gmod"] = check_vec(got["gmod"][..., None], ref["gmod"][..., None], "gmod", rho=ref["f"])
+    hn = np.sqrt(sum(ref[k] ** 2 for k in hk))
+    err = np.abs(got["lap"] - ref["lap"]) / np.maximum(np.maximum(hn, 1e-4 * np.abs(ref["f"])), 1e-20)
+    assert err.max() <= cases.TOL_DER, f"lap {err.max():.3e}"
+    return e
+
+
+@pytest.mark.parametrize("name,n", [("h2o-aqz", 24), ("benzene-adz", 20), ("hooh-atz", 20), ("h2o-wfx", 20)])
+def test_cube_real_molecules(G, O, name, n):
+    f = cases.golden_wfn(name)
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, n, margin=3.0)
+    ref = _ofield(O, f, st).cube(x0, xd, nn)
+    fld = G.WfnField(f, st)
+    got = fld.cube(x0, xd, nn)
+    e = _compare_cube(got, ref)
+    print(name, fld.config(), e)
+
+
+def test_cube_cell_grid_ragged(G, O):
+    """CUBE CELL-like grid over the whole molecular cell (mostly vacuum: exact zeros) with ragged sizes."""
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("h2o-aqz")
+    st = cases.mol_structure(f)
+    o, xd, nn = drivers.cube_grid(st, (13, 7, 10))
+    ref = _ofield(O, f, st).cube(o, xd, nn)
+    got = G.WfnField(f, st).cube(o, xd, nn)
+    _compare_cube(got, ref)
+    assert (ref["f"] == 0).any()
+
+
+@pytest.mark.parametrize("cfg", [2, 3, 4])
+@pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
+def test_cube_synthetic_all_configs(G, O, cfg, variant):
+    """24-atom def2-TZVP-shaped synthetic molecule through the M / L / L1 tensor-core tile configurations."""
+    from critic2_b200 import synth
+    f = synth.small_synthetic(uhf=(variant != "rhf"), with_edf=(variant != "rhf"))
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, (18, 14, 12), margin=3.0)
+    ref = _ofield(O, f, st).cube(x0, xd, nn)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    assert fld.config()["cfg"] == cfg
+    got = fld.cube(x0, xd, nn)
+    print(cfg, variant, _compare_cube(got, ref))
+
+
+@pytest.mark.parametrize("nder", [0, 1])
+def test_lower_nder(G, O, nder):
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, 12, margin=2.0)
+    pts = np.array([x0 + xd @ np.array([i, j, k], float) for k in range(nn[2]) for j in range(nn[1]) for i in range(nn[0])])
+    ref = _ofield(O, f, st).grd_points(pts, nder=nder, periodic=False)
+    got = G.WfnField(f, st).cube(x0, xd, nn, nder=nder)
+    check_rho(got["f"].reshape(-1), ref[:, 0])
+    if nder == 1:
+        check_vec(np.stack([got[k].reshape(-1) for k in ("gx", "gy", "gz")], -1), ref[:, 1:4], "grad", rho=ref[:, 0])
+    else:
+        assert not got["gx"].any()
+
+
+def test_points_and_nucleus(G, O):
+    """field%grd on a point list, including a point on a nucleus (gradient zeroed, fieldmod@proc.f90:836-838)."""
+    f = cases.golden_wfn("h2o-aqz")
+    st = cases.mol_structure(f)
+    rng = np.random.default_rng(3)
+    pts = st.r[rng.integers(0, 3, 700)] + rng.normal(0, 1.5, (700, 3))
+    pts[:3] = st.r
+    pts[3] = st.r[0] + np.array([3e-6, 0, 0])
+    pts[4] = st.r[0] + np.array([3e-5, 0, 0])
+    ref = _ofield(O, f, st).grd_points(pts, nder=2, periodic=True)
+    got = G.WfnField(f, st).points(pts, nder=2, periodic=True)
+    assert np.array_equal(got[:, 15], ref[:, 15])
+    assert ref[:4, 15].all() and not ref[4, 15]
+    check_rho(got[:, 0], ref[:, 0])
+    check_vec(got[:, 1:4], ref[:, 1:4], "grad", rho=ref[:, 0])
+    check_vec(got[:, 4:13], ref[:, 4:13], "hess", rho=ref[:, 0])
+    assert not got[:4, 1:4].any() and got[:4, 13].max() == 0.0
+
+
+def _nci_compare(got_rho, got_grad, ref_rho, ref_grad):
+    # |crho| = 100*rho ; sign = sign(lambda2)
+    check_rho(np.abs(got_rho), np.abs(ref_rho), "crho magnitude")
+    err = np.abs(got_grad - ref_grad) / np.maximum(np.abs(ref_grad), 1e-20)
+    big = ref_grad < 1e40
+    assert err[big].max() <= cases.TOL_DER, f"RDG {err[big].max():.3e}"
+    flips = np.sign(got_rho) != np.sign(ref_rho)
+    return int(flips.sum())
+
+
+def test_nci_benzene(G, O):
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(22, 20, 18))
+    of = _ofield(O, f, st)
+    rrho, rgrad, _ = of.nci(x0, xmat, ns)
+    fld = G.WfnField(f, st)
+    crho, cgrad, _ = fld.nci(x0, xmat, ns)
+    nflip = _nci_compare(crho, cgrad, rrho, rgrad)
+    assert nflip == 0, f"{nflip} sign(lambda2) flips"
+    # cutoff pass: identical classification
+    rg = rgrad.copy()
+    rsums, rdat = O.nci_cutoffs(rrho.copy(), rg)
+    cg = cgrad.reshape(-1).copy()
+    sums, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg)
+    assert ndat == len(rdat)
+    assert np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
+    np.testing.assert_allclose(dat, rdat, rtol=1e-8, atol=0)
+
+
+def test_nci_void_with_promolecular(G, O):
+    """NCIPLOT with VOID: rhoat from the promolecular field f(0) (nci@proc.f90:529-531) and the void sums (:573-582)."""
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("h2o-aqz")
+    st = cases.mol_structure(f)
+    tabs = cases.tables()
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(16, 15, 14))
+    env = O.Environ(st)
+    of = O.Field(env, wfn=O.Wfn(f))
+    op = O.Field(env, grids=O.Grid1Set(tabs))
+    rrho, rgrad, rat = of.nci(x0, xmat, ns, promol=op)
+    fld, pro = G.WfnField(f, st), G.PromolField(st, tabs)
+    crho, cgrad, cat = fld.nci(x0, xmat, ns, promol=pro)
+    assert _nci_compare(crho, cgrad, rrho, rgrad) == 0
+    check_rho(cat, rat, "rhoat")
+    rg = rgrad.copy()
+    rsums, rdat = O.nci_cutoffs(rrho.copy(), rg, rat, rho_void=0.05, omega=st.omega)
+    cg = cgrad.reshape(-1).copy()
+    sums, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg, cat.reshape(-1), rho_void=0.05, omega=st.omega)
+    assert ndat == len(rdat)
+    np.testing.assert_allclose(sums, rsums, rtol=1e-10)
+    assert np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
+
+
+def test_promolecular_quartz_cube(G, O):
+    """Promolecular density of alpha-quartz (periodic, images) with gradient and Hessian on a ragged whole-cell grid."""
+    from critic2_b200 import drivers
+    st = cases.quartz(1)
+    tabs = cases.tables()
+    env = O.Environ(st)
+    of = O.Field(env, grids=O.Grid1Set(tabs))
+    o, xd, nn = drivers.cube_grid(st, (20, 18, 21))
+    ref = of.cube(o, xd, nn, periodic=True)
+    pro = G.PromolField(st, tabs)
+    got = pro.cube(o, xd, nn, periodic=True)
+    print(_compare_cube(got, ref))
+
+
+def test_promolecular_grid_and_nci(G, O):
+    st = cases.quartz(1)
+    tabs = cases.tables()
+    env = O.Environ(st)
+    grids = O.Grid1Set(tabs)
+    n = (17, 16, 19)
+    ref = O.promolecular_grid(env, grids, n)
+    pro = G.PromolField(st, tabs)
+    got = pro.promolecular_grid(n)
+    check_rho(got, ref, "promolecular_grid")
+    # NCIPLOT on the promolecular density (iref = 0), periodic cell
+    from critic2_b200 import drivers
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(12, 13, 14))
+    of = O.Field(env, grids=grids)
+    rrho, rgrad, _ = of.nci(x0, xmat, ns)
+    crho, cgrad, _ = pro.nci(x0, xmat, ns)
+    assert _nci_compare(crho, cgrad, rrho, rgrad) == 0
+
+
+def test_promolecular_molecule_fragment(G, O):
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    tabs = cases.tables()
+    mask = np.zeros(st.ncell, np.uint8)
+    mask[:6] = 1
+    env = O.Environ(st)
+    x0, xd, nn = cases.bbox_grid(st, (15, 14, 9), margin=5.0)
+    for fm in (None, mask):
+        of = O.Field(env, grids=O.Grid1Set(tabs), fragmask=fm)
+        ref = of.cube(x0, xd, nn)
+        got = G.PromolField(st, tabs, fragmask=fm).cube(x0, xd, nn)
+        _compare_cube(got, ref)
