@@ -52,6 +52,11 @@ def lib():
         L.c2gpu_eval_grid.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint, C.POINTER(dp)]
         L.c2gpu_eval_grid_dev.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p),
                                           C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_eval_grid_dev_part.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint,
+                                               C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_layer_height.argtypes = [C.c_void_p]
+        L.c2gpu_nci_grid_dev_part.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_nci_grid.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, dp, dp, dp]
         L.c2gpu_nci_grid_dev.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_int, C.c_int, C.c_void_p]
@@ -164,6 +169,19 @@ class _Field:
         _check(lib().c2gpu_eval_grid_dev(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs,
                                          iz0, int(nna[2]) if iz1 is None else iz1, C.c_void_p(stream)))
 
+    def cube_dev_part(self, x0, xd, nn, outs, props, part: int, nparts: int, nder: int = 2, periodic: bool = False,
+                      stream: int = 0):
+        """Like cube_dev for the interleaved z layers (layer % nparts == part): the multi-GPU decomposition."""
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        names = [p for p in PROPS if p in props]
+        mask = sum(1 << PROPS.index(p) for p in names)
+        ptrs = (C.c_void_p * len(outs))(*[C.c_void_p(t.data_ptr()) for t in outs])
+        _check(lib().c2gpu_eval_grid_dev_part(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs,
+                                              part, nparts, C.c_void_p(stream)))
+
+    def layer_height(self) -> int:
+        return int(lib().c2gpu_layer_height(self.handle))
+
     # -- nciplot evaluation loop, nci@proc.f90:499-561 ----------------------------------------------------------
     def nci(self, x0, xmat, nstep, promol: "_Field | None" = None):
         """Returns crho, cgrad[, rhoat] as (n1, n2, n3) arrays, z fastest (the reference's crho(k,j,i))."""
@@ -183,6 +201,15 @@ class _Field:
                                         _i(nna), C.c_void_p(crho.data_ptr()), C.c_void_p(cgrad.data_ptr()),
                                         C.c_void_p(rhoat.data_ptr()) if rhoat is not None else None, i0,
                                         int(nna[0]) if i1 is None else i1, C.c_void_p(stream)))
+
+    def nci_dev_part(self, x0, xmat, nstep, crho, cgrad, part: int, nparts: int, rhoat=None,
+                     promol: "_Field | None" = None, stream: int = 0):
+        x0a, xda, nna = _grid_args(x0, xmat, nstep)
+        _check(lib().c2gpu_nci_grid_dev_part(self.handle, promol.handle if promol is not None else None, _d(x0a),
+                                             _d(xda), _i(nna), C.c_void_p(crho.data_ptr()),
+                                             C.c_void_p(cgrad.data_ptr()),
+                                             C.c_void_p(rhoat.data_ptr()) if rhoat is not None else None, part, nparts,
+                                             C.c_void_p(stream)))
 
     # -- field%grd on a point list, fieldmod@proc.f90:613-842 ---------------------------------------------------
     def points(self, pts, nder: int = 2, periodic: bool = True):

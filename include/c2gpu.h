@@ -84,6 +84,13 @@ int c2gpu_eval_grid(void *h, const double x0[3], const double xd[9], const int n
 int c2gpu_eval_grid_dev(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
                         unsigned outmask, double *const *out_dev, int iz0, int iz1, void *stream);
 
+/* the layers of height 8 along z with (layer index mod nparts == part), into full-size DEVICE arrays: the
+   interleaved (load-balanced) slab decomposition the host variant uses across devices, for one-process-per-GPU hosts */
+int c2gpu_eval_grid_dev_part(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
+                             unsigned outmask, double *const *out_dev, int part, int nparts, void *stream);
+/* height of those layers for handle h (8 for wavefunction fields, 4 for promolecular fields) */
+int c2gpu_layer_height(void *h);
+
 /* ---- NCIPLOT: evaluation loop src/nci@proc.f90:499-561, cutoff pass :569-604 ---------------------------------- */
 /* crho/cgrad/rhoat are (0:n3-1,0:n2-1,0:n1-1): z fastest, x slowest (:458-469).  hpromol/rhoat may be NULL. */
 int c2gpu_nci_grid(void *href, void *hpromol, const double x0[3], const double xmat[9], const int nstep[3],
@@ -91,6 +98,10 @@ int c2gpu_nci_grid(void *href, void *hpromol, const double x0[3], const double x
 /* slab [i0,i1) of the slowest (x) index into full-size DEVICE arrays */
 int c2gpu_nci_grid_dev(void *href, void *hpromol, const double x0[3], const double xmat[9], const int nstep[3],
                        double *crho_dev, double *cgrad_dev, double *rhoat_dev, int i0, int i1, void *stream);
+/* interleaved layers along x (see c2gpu_eval_grid_dev_part) */
+int c2gpu_nci_grid_dev_part(void *href, void *hpromol, const double x0[3], const double xmat[9], const int nstep[3],
+                            double *crho_dev, double *cgrad_dev, double *rhoat_dev, int part, int nparts,
+                            void *stream);
 /* Cutoff pass (nfrag = 0).  Modifies cgrad in place; sums[3] = sumq,sumqp,sumv (scaled by omega/N, :600-603);
    *ndat = number of (rho,s) pairs of the .dat file; dat (2*maxdat doubles, may be NULL) receives the first maxdat
    pairs in the reference's loop order.  rho_void <= 0 disables the VOID test (rhoat may then be NULL). */

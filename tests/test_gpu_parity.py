@@ -64,7 +64,7 @@ def test_cube_cell_grid_ragged(G, O):
     """CUBE CELL-like grid over the whole molecular cell (mostly vacuum: exact zeros) with ragged sizes."""
     from critic2_b200 import drivers
     f = cases.golden_wfn("h2o-aqz")
-    st = cases.mol_structure(f)
+    st = cases.mol_structure(f, border=40.0)
     o, xd, nn = drivers.cube_grid(st, (13, 7, 10))
     ref = _ofield(O, f, st).cube(o, xd, nn)
     got = G.WfnField(f, st).cube(o, xd, nn)
@@ -128,7 +128,11 @@ def test_points_and_nucleus(G, O):
 def _nci_compare(got_rho, got_grad, ref_rho, ref_grad):
     # |crho| = 100*rho ; sign = sign(lambda2)
     check_rho(np.abs(got_rho), np.abs(ref_rho), "crho magnitude")
-    err = np.abs(got_grad - ref_grad) / np.maximum(np.abs(ref_grad), 1e-20)
+    # RDG = |grad rho| / (c rho^(4/3)): where |grad rho| vanishes by symmetry (critical points on grid nodes) the
+    # gradient floor of cases.check_vec (1e-4*rho) carries over as 1e-4*rho/(c rho^(4/3))
+    rho = np.maximum(np.abs(ref_rho) / 100.0, 1e-80)
+    floor = 1e-4 * rho / (2.0 * (3.0 * np.pi ** 2) ** (1.0 / 3.0) * rho ** (4.0 / 3.0))
+    err = np.abs(got_grad - ref_grad) / np.maximum(np.abs(ref_grad), floor)
     big = ref_grad < 1e40
     assert err[big].max() <= cases.TOL_DER, f"RDG {err[big].max():.3e}"
     flips = np.sign(got_rho) != np.sign(ref_rho)
@@ -153,7 +157,10 @@ def test_nci_benzene(G, O):
     sums, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg)
     assert ndat == len(rdat)
     assert np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
-    np.testing.assert_allclose(dat, rdat, rtol=1e-8, atol=0)
+    np.testing.assert_allclose(dat[:, 0], rdat[:, 0], rtol=1e-10, atol=0)
+    rho = np.maximum(np.abs(rdat[:, 0]), 1e-80)
+    floor = 1e-4 * rho / (2.0 * (3.0 * np.pi ** 2) ** (1.0 / 3.0) * rho ** (4.0 / 3.0))
+    assert (np.abs(dat[:, 1] - rdat[:, 1]) / np.maximum(rdat[:, 1], floor)).max() <= cases.TOL_DER
 
 
 def test_nci_void_with_promolecular(G, O):
