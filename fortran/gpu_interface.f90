@@ -1,0 +1,326 @@
+! gpu_interface.f90 -- iso_c_binding shim between critic2's Fortran drivers and libc2gpu (include/c2gpu.h).
+!
+! Sits in src/ next to c_interface_module.f90 and follows the in-tree Fortran->C pattern
+! (interface ... bind(c) blocks, src/crystalmod@proc.f90:3170-3186; implementation in C, src/doqhull.c).
+! The host program stays Fortran: this module only flattens type(molwfn) / type(environ) / agrid(:) into the
+! plain arrays of the C ABI and forwards the grid descriptors of the three evaluation loops it replaces:
+!   rhoplot_cube        src/rhoplot@proc.f90:582-631
+!   nciplot             src/nci@proc.f90:499-561 (evaluation) and :569-604 (cutoff pass)
+!   promolecular_grid   src/crystalmod@proc.f90:5118-5158
+! Status convention: 0 ok; -1 unsupported input (the caller keeps its OpenMP loop); >0 error -> ferror(faterr).
+!
+! NOT compiled in the authoring container (no Fortran compiler exists there); see INTEGRATION.md.
+module gpu_interface
+  use iso_c_binding, only: c_int, c_long, c_double, c_ptr, c_char, c_null_ptr, c_null_char, c_associated, c_loc
+  implicit none
+  private
+
+  public :: gpu_enabled, gpu_init, gpu_end
+  public :: gpu_wfn_handle, gpu_promol_handle, gpu_destroy
+  public :: gpu_cube, gpu_nciplot, gpu_nci_cutoffs, gpu_promolecular_grid
+
+  logical, save :: gpu_enabled = .false. !< set by the GPU keyword (global@proc.f90, critic_setvariables)
+
+  interface
+     function c2gpu_init(ndev_req,ndev) bind(c,name="c2gpu_init") result(ierr)
+       import :: c_int
+       integer(c_int), value :: ndev_req
+       integer(c_int) :: ndev
+       integer(c_int) :: ierr
+     end function c2gpu_init
+     function c2gpu_finalize() bind(c,name="c2gpu_finalize") result(ierr)
+       import :: c_int
+       integer(c_int) :: ierr
+     end function c2gpu_finalize
+     function c2gpu_last_error(buf,len) bind(c,name="c2gpu_last_error") result(ierr)
+       import :: c_int, c_char
+       character(kind=c_char) :: buf(*)
+       integer(c_int), value :: len
+       integer(c_int) :: ierr
+     end function c2gpu_last_error
+     function c2gpu_wfn_create(natom,xyz,npri,icenter,itype,expo,dran,nmoocc,ldc,cmo,occ,wfntyp,nalpha,&
+        nedf,icenter_edf,itype_edf,e_edf,c_edf,dran_edf,ismolecule,m_x2c,m_c2x,handle) &
+        bind(c,name="c2gpu_wfn_create") result(ierr)
+       import :: c_int, c_double, c_ptr
+       integer(c_int), value :: natom, npri, nmoocc, ldc, wfntyp, nalpha, nedf, ismolecule
+       real(c_double) :: xyz(3,*), expo(*), dran(*), cmo(ldc,*), occ(*), e_edf(*), c_edf(*), dran_edf(*)
+       integer(c_int) :: icenter(*), itype(*), icenter_edf(*), itype_edf(*)
+       real(c_double) :: m_x2c(3,3), m_c2x(3,3)
+       type(c_ptr) :: handle
+       integer(c_int) :: ierr
+     end function c2gpu_wfn_create
+     function c2gpu_promol_create(nenv,ncell,xyz_env,ispc,cidx,nspc,zspc,ngrid,a,b,cutrad,tab_r,tab_f,tab_fp,&
+        tab_fpp,ismolecule,m_x2c,m_c2x,m_xr2c,m_c2xr,fragmask,handle) bind(c,name="c2gpu_promol_create") result(ierr)
+       import :: c_int, c_double, c_ptr
+       integer(c_int), value :: nenv, ncell, nspc, ismolecule
+       real(c_double) :: xyz_env(3,*), a(*), b(*), cutrad(*), tab_r(*), tab_f(*), tab_fp(*), tab_fpp(*)
+       integer(c_int) :: ispc(*), cidx(*), zspc(*), ngrid(*)
+       real(c_double) :: m_x2c(3,3), m_c2x(3,3), m_xr2c(3,3), m_c2xr(3,3)
+       type(c_ptr), value :: fragmask
+       type(c_ptr) :: handle
+       integer(c_int) :: ierr
+     end function c2gpu_promol_create
+     function c2gpu_destroy(handle) bind(c,name="c2gpu_destroy") result(ierr)
+       import :: c_int, c_ptr
+       type(c_ptr), value :: handle
+       integer(c_int) :: ierr
+     end function c2gpu_destroy
+     function c2gpu_eval_grid(h,x0,xd,nn,nder,periodic,outmask,out) bind(c,name="c2gpu_eval_grid") result(ierr)
+       import :: c_int, c_double, c_ptr
+       type(c_ptr), value :: h
+       real(c_double) :: x0(3), xd(3,3)
+       integer(c_int) :: nn(3)
+       integer(c_int), value :: nder, periodic, outmask
+       type(c_ptr) :: out(*)
+       integer(c_int) :: ierr
+     end function c2gpu_eval_grid
+     function c2gpu_nci_grid(href,hpromol,x0,xmat,nstep,crho,cgrad,rhoat) bind(c,name="c2gpu_nci_grid") result(ierr)
+       import :: c_int, c_double, c_ptr
+       type(c_ptr), value :: href, hpromol
+       real(c_double) :: x0(3), xmat(3,3)
+       integer(c_int) :: nstep(3)
+       real(c_double) :: crho(*), cgrad(*)
+       type(c_ptr), value :: rhoat
+       integer(c_int) :: ierr
+     end function c2gpu_nci_grid
+     function c2gpu_nci_cutoffs(npts,crho,cgrad,rhoat,rhocut,dimcut,rhoplot,srhorange,onlyneg,rho_void,omega,&
+        sums,ndat,dat,maxdat) bind(c,name="c2gpu_nci_cutoffs") result(ierr)
+       import :: c_int, c_long, c_double, c_ptr
+       integer(c_long), value :: npts, maxdat
+       real(c_double) :: crho(*), cgrad(*)
+       type(c_ptr), value :: rhoat, dat
+       real(c_double), value :: rhocut, dimcut, rhoplot, rho_void, omega
+       real(c_double) :: srhorange(2), sums(3)
+       integer(c_int), value :: onlyneg
+       integer(c_long) :: ndat
+       integer(c_int) :: ierr
+     end function c2gpu_nci_cutoffs
+     function c2gpu_promol_grid(h,n,out) bind(c,name="c2gpu_promol_grid") result(ierr)
+       import :: c_int, c_double, c_ptr
+       type(c_ptr), value :: h
+       integer(c_int) :: n(3)
+       real(c_double) :: out(*)
+       integer(c_int) :: ierr
+     end function c2gpu_promol_grid
+  end interface
+
+contains
+
+  !> Turn a non-zero status into the reference's error convention (tools_io ferror).  -1 is not an error.
+  subroutine gpu_check(routine,ierr)
+    use tools_io, only: ferror, faterr
+    character*(*), intent(in) :: routine
+    integer(c_int), intent(in) :: ierr
+    character(kind=c_char) :: buf(512)
+    character(len=512) :: msg
+    integer :: i, idum
+    if (ierr <= 0) return
+    idum = c2gpu_last_error(buf,512_c_int)
+    msg = ""
+    do i = 1, 512
+       if (buf(i) == c_null_char) exit
+       msg(i:i) = buf(i)
+    end do
+    call ferror(routine,"GPU module: " // trim(msg),faterr)
+  end subroutine gpu_check
+
+  subroutine gpu_init(ndev)
+    integer, intent(out) :: ndev
+    integer(c_int) :: n, ierr
+    ierr = c2gpu_init(0_c_int,n)
+    call gpu_check("gpu_init",ierr)
+    ndev = n
+    gpu_enabled = (ierr == 0 .and. n > 0)
+  end subroutine gpu_init
+
+  subroutine gpu_end()
+    integer(c_int) :: ierr
+    ierr = c2gpu_finalize()
+    gpu_enabled = .false.
+  end subroutine gpu_end
+
+  !> Device image of a wavefunction field (called from field_new after complete_struct; freed in field_end).
+  !> Returns c_null_ptr when the input is unsupported (STO basis, crystal environment): the caller keeps grd.
+  function gpu_wfn_handle(w,c) result(h)
+    use wfn_private, only: molwfn, wfn_frac
+    use crystalmod, only: crystal
+    type(molwfn), intent(in), target :: w
+    type(crystal), intent(in) :: c
+    type(c_ptr) :: h
+    real(c_double), allocatable :: xyz(:,:)
+    integer(c_int) :: ierr, ldc
+    integer :: i
+    real(c_double) :: dumr(1)
+    integer(c_int) :: dumi(1)
+    h = c_null_ptr
+    if (w%issto .or. .not.c%ismolecule) return
+    allocate(xyz(3,w%env%ncell))
+    do i = 1, w%env%ncell
+       xyz(:,i) = w%env%at(i)%r
+    end do
+    ldc = size(w%cmo,1)
+    if (w%nedf > 0) then
+       ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
+          int(w%nmoocc,c_int),ldc,w%cmo,w%occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),int(w%nedf,c_int),&
+          w%icenter_edf,w%itype_edf,w%e_edf,w%c_edf,w%dran_edf,1_c_int,c%m_x2c,c%m_c2x,h)
+    else
+       ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
+          int(w%nmoocc,c_int),ldc,w%cmo,w%occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),0_c_int,&
+          dumi,dumi,dumr,dumr,dumr,1_c_int,c%m_x2c,c%m_c2x,h)
+    end if
+    if (ierr == -1) h = c_null_ptr
+    call gpu_check("gpu_wfn_handle",ierr)
+  end function gpu_wfn_handle
+
+  !> Device image of the promolecular field f(0): environment atoms + agrid(:) radial tables.
+  function gpu_promol_handle(c,fr) result(h)
+    use crystalmod, only: crystal
+    use fragmentmod, only: fragment
+    use grid1mod, only: agrid
+    use global, only: cutrad
+    use param, only: maxzat
+    type(crystal), intent(in) :: c
+    type(fragment), intent(in), optional :: fr
+    type(c_ptr) :: h
+    real(c_double), allocatable :: xyz(:,:), a(:), b(:), cut(:), tr(:), tf(:), tfp(:), tfpp(:)
+    integer(c_int), allocatable :: ispc(:), cidx(:), zspc(:), ngrid(:)
+    character(kind=c_char), allocatable, target :: mask(:)
+    type(c_ptr) :: pmask
+    integer :: i, is, iz, ntot, n0
+    integer(c_int) :: ierr
+    h = c_null_ptr
+    pmask = c_null_ptr
+    allocate(xyz(3,c%env%n),ispc(c%env%n),cidx(c%env%n))
+    do i = 1, c%env%n
+       xyz(:,i) = c%env%at(i)%r
+       ispc(i) = c%env%at(i)%is
+       cidx(i) = c%env%at(i)%cidx
+    end do
+    allocate(zspc(c%nspc),ngrid(c%nspc),a(c%nspc),b(c%nspc),cut(c%nspc))
+    ntot = 0
+    do is = 1, c%nspc
+       iz = c%spc(is)%z
+       zspc(is) = iz
+       ngrid(is) = 0; a(is) = 0d0; b(is) = 1d0; cut(is) = 0d0
+       if (iz > 0 .and. iz <= maxzat) then
+          cut(is) = cutrad(iz)
+          if (agrid(iz)%isinit) then
+             ngrid(is) = agrid(iz)%ngrid; a(is) = agrid(iz)%a; b(is) = agrid(iz)%b
+          end if
+       end if
+       ntot = ntot + ngrid(is)
+    end do
+    allocate(tr(max(ntot,1)),tf(max(ntot,1)),tfp(max(ntot,1)),tfpp(max(ntot,1)))
+    n0 = 0
+    do is = 1, c%nspc
+       if (ngrid(is) == 0) cycle
+       iz = zspc(is)
+       tr(n0+1:n0+ngrid(is)) = agrid(iz)%r(1:ngrid(is))
+       tf(n0+1:n0+ngrid(is)) = agrid(iz)%f(1:ngrid(is))
+       tfp(n0+1:n0+ngrid(is)) = agrid(iz)%fp(1:ngrid(is))
+       tfpp(n0+1:n0+ngrid(is)) = agrid(iz)%fpp(1:ngrid(is))
+       n0 = n0 + ngrid(is)
+    end do
+    if (present(fr)) then
+       ! type_promol_frag: one byte per cell atom, 1 = atom belongs to the fragment (environmod@proc.f90:1287-1290)
+       allocate(mask(c%ncel))
+       mask = achar(0)
+       do i = 1, fr%nat
+          mask(fr%at(i)%cidx) = achar(1)
+       end do
+       pmask = c_loc(mask(1))
+    end if
+    ierr = c2gpu_promol_create(int(c%env%n,c_int),int(c%ncel,c_int),xyz,ispc,cidx,int(c%nspc,c_int),zspc,ngrid,&
+       a,b,cut,tr,tf,tfp,tfpp,merge(1_c_int,0_c_int,c%ismolecule),c%m_x2c,c%m_c2x,c%m_xr2c,c%m_c2xr,pmask,h)
+    if (ierr == -1) h = c_null_ptr
+    call gpu_check("gpu_promol_handle",ierr)
+  end function gpu_promol_handle
+
+  subroutine gpu_destroy(h)
+    type(c_ptr), intent(inout) :: h
+    integer(c_int) :: ierr
+    if (c_associated(h)) ierr = c2gpu_destroy(h)
+    h = c_null_ptr
+  end subroutine gpu_destroy
+
+  !> Replacement of the rhoplot_cube evaluation loop (rhoplot@proc.f90:587-631) for ONE property nti.
+  !> ok = .false. means "unsupported": the caller runs its own loop.
+  subroutine gpu_cube(h,x0,xd,nn,periodic,nti,lf,ok)
+    type(c_ptr), intent(in) :: h
+    real(c_double), intent(in) :: x0(3), xd(3,3)
+    integer, intent(in) :: nn(3), nti   !< nti: 0 f, 1 gx, 2 gy, 3 gz, 4 gmod, 5 hxx ... 10 hzz, 11 lap (:488-523)
+    logical, intent(in) :: periodic
+    real(c_double), intent(inout), target :: lf(:,:,:)
+    logical, intent(out) :: ok
+    type(c_ptr) :: out(1)
+    integer(c_int) :: ierr, n(3)
+    ok = .false.
+    if (.not.gpu_enabled .or. .not.c_associated(h)) return
+    n = int(nn,c_int)
+    out(1) = c_loc(lf(1,1,1))
+    ierr = c2gpu_eval_grid(h,x0,xd,n,2_c_int,merge(1_c_int,0_c_int,periodic),int(ishft(1,nti),c_int),out)
+    call gpu_check("rhoplot_cube",ierr)
+    ok = (ierr == 0)
+  end subroutine gpu_cube
+
+  !> Replacement of the nciplot evaluation loop (nci@proc.f90:499-561); crho/cgrad(0:n3-1,0:n2-1,0:n1-1).
+  subroutine gpu_nciplot(href,hpromol,x0,xmat,nstep,crho,cgrad,rhoat,ok)
+    type(c_ptr), intent(in) :: href, hpromol
+    real(c_double), intent(in) :: x0(3), xmat(3,3)
+    integer, intent(in) :: nstep(3)
+    real(c_double), intent(inout) :: crho(0:,0:,0:), cgrad(0:,0:,0:)
+    real(c_double), intent(inout), target, optional :: rhoat(0:,0:,0:)
+    logical, intent(out) :: ok
+    integer(c_int) :: ierr, n(3)
+    type(c_ptr) :: pat
+    ok = .false.
+    if (.not.gpu_enabled .or. .not.c_associated(href)) return
+    n = int(nstep,c_int)
+    pat = c_null_ptr
+    if (present(rhoat) .and. c_associated(hpromol)) pat = c_loc(rhoat(0,0,0))
+    ierr = c2gpu_nci_grid(href,hpromol,x0,xmat,n,crho,cgrad,pat)
+    call gpu_check("nciplot",ierr)
+    ok = (ierr == 0)
+  end subroutine gpu_nciplot
+
+  !> Replacement of the nciplot cutoff pass (nci@proc.f90:569-604, nfrag = 0): void sums, .dat pairs, cgrad masking.
+  subroutine gpu_nci_cutoffs(crho,cgrad,rhoat,rhocut,dimcut,rhoplot,srhorange,onlyneg,rho_void,omega,&
+     sumq,sumqp,sumv,ndat,dat,ok)
+    real(c_double), intent(inout) :: crho(0:,0:,0:), cgrad(0:,0:,0:)
+    real(c_double), intent(in), target, optional :: rhoat(0:,0:,0:)
+    real(c_double), intent(in) :: rhocut, dimcut, rhoplot, srhorange(2), rho_void, omega
+    logical, intent(in) :: onlyneg
+    real(c_double), intent(out) :: sumq, sumqp, sumv
+    integer(c_long), intent(out) :: ndat
+    real(c_double), intent(inout), target :: dat(:,:)   !< (2,maxdat): rho, s pairs of the .dat file (:593-595)
+    logical, intent(out) :: ok
+    real(c_double) :: sums(3)
+    integer(c_int) :: ierr
+    type(c_ptr) :: pat
+    ok = .false.
+    if (.not.gpu_enabled) return
+    pat = c_null_ptr
+    if (present(rhoat)) pat = c_loc(rhoat(0,0,0))
+    ierr = c2gpu_nci_cutoffs(int(size(crho),c_long),crho,cgrad,pat,rhocut,dimcut,rhoplot,srhorange,&
+       merge(1_c_int,0_c_int,onlyneg),rho_void,omega,sums,ndat,c_loc(dat(1,1)),int(size(dat,2),c_long))
+    call gpu_check("nciplot",ierr)
+    sumq = sums(1); sumqp = sums(2); sumv = sums(3)
+    ok = (ierr == 0)
+  end subroutine gpu_nci_cutoffs
+
+  !> Replacement of the promolecular_grid loop (crystalmod@proc.f90:5143-5158): f(n1,n2,n3), nder = 0.
+  subroutine gpu_promolecular_grid(h,n,f,ok)
+    type(c_ptr), intent(in) :: h
+    integer, intent(in) :: n(3)
+    real(c_double), intent(inout) :: f(:,:,:)
+    logical, intent(out) :: ok
+    integer(c_int) :: ierr, nn(3)
+    ok = .false.
+    if (.not.gpu_enabled .or. .not.c_associated(h)) return
+    nn = int(n,c_int)
+    ierr = c2gpu_promol_grid(h,nn,f)
+    call gpu_check("promolecular_grid",ierr)
+    ok = (ierr == 0)
+  end subroutine gpu_promolecular_grid
+
+end module gpu_interface

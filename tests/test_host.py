@@ -1,0 +1,145 @@
+"""CPU tests of the host side: the C-ABI library loads and exports what include/c2gpu.h declares, the loaders'
+tables agree with the oracle's independent complete_struct, the driver grid definitions follow the reference, and the
+multi-GPU slab logic works over a world_size-2 gloo group.  No compute call is made on the (absent) GPU."""
+import ctypes
+import os
+import re
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_abi_library_exports_every_declared_symbol():
+    from critic2_b200 import gpu
+    L = ctypes.CDLL(gpu.LIB_PATH)
+    hdr = open(os.path.join(ROOT, "include", "c2gpu.h")).read()
+    names = sorted(set(re.findall(r"^\s*(?:int|long)\s+(c2gpu_\w+)\s*\(", hdr, re.M)))
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/c2gpu.h but not exported"
+    # the Fortran binding names the same symbols
+    f90 = open(os.path.join(ROOT, "fortran", "gpu_interface.f90")).read()
+    for n in re.findall(r'name="(c2gpu_\w+)"', f90):
+        assert n in names, f"fortran/gpu_interface.f90 binds unknown symbol {n}"
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from critic2_b200 import gpu
+    f = cases.golden_wfn("h2o-wfx")
+    st = cases.mol_structure(f)
+    with pytest.raises(gpu.C2GpuError):
+        gpu.WfnField(f, st)
+    with pytest.raises(gpu.C2GpuError):
+        gpu.nci_cutoffs(np.zeros(8), np.zeros(8))
+
+
+def test_product_never_imports_the_oracle():
+    for dp, _, files in os.walk(os.path.join(ROOT, "critic2_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".inc")):
+                src = open(os.path.join(dp, fn)).read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", src, re.M), fn
+                assert "liboracle" not in src and "oracle.h" not in src, fn
+
+
+def test_complete_struct_tables_match_oracle():
+    import oracle
+    for name in ("h2o-aqz", "benzene-adz", "hooh-atz"):
+        f = cases.golden_wfn(name)
+        dran, spc, lmax, icord, lo, hi = oracle.Wfn(f).tables()
+        np.testing.assert_array_equal(dran, f.dran)
+        np.testing.assert_array_equal(spc, f.spcutoff)
+        np.testing.assert_array_equal(lmax, f.lmax)
+        np.testing.assert_array_equal(icord, f.icord)
+        np.testing.assert_array_equal(lo, f.iprilo)
+        np.testing.assert_array_equal(hi, f.iprihi)
+
+
+def test_wfx_roundtrip_and_synthetic_shapes(tmp_path):
+    from critic2_b200 import synth, wfn
+    f = synth.small_synthetic(with_edf=True)
+    p = str(tmp_path / "s.wfx")
+    wfn.write_wfx(f, p)
+    g = wfn.read_wfx(p)
+    assert g.npri == f.npri and g.nmoocc == f.nmoocc and g.nedf == f.nedf
+    np.testing.assert_allclose(g.cmo, f.cmo, rtol=1e-14)
+    np.testing.assert_allclose(g.e, f.e, rtol=1e-14)
+    np.testing.assert_array_equal(g.itype, f.itype)
+    f4 = synth.config4()
+    assert (f4.natom, f4.npri, f4.nmoocc) == (500, 12600, 780)
+
+
+def test_driver_grid_definitions():
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    o, xd, nn = drivers.cube_grid(st, (10, 12, 14))
+    np.testing.assert_allclose(o, 0)                      # CUBE CELL: x0 = cell origin
+    np.testing.assert_allclose(xd @ nn.astype(float), st.m_x2c @ np.ones(3))   # end point excluded
+    x0, xmat, ns = drivers.nci_grid(st)                   # xinc 0.1 bohr default
+    assert np.allclose(np.diag(xmat), 0.1) and (ns > 50).all()
+    lo = st.m_x2c @ st.molborder
+    np.testing.assert_allclose(x0, lo, rtol=1e-12)
+    q = cases.quartz(1)
+    x0, xmat, ns = drivers.nci_grid(q, nstep=(10, 10, 11))
+    np.testing.assert_allclose(xmat[:, 2] * 11, q.m_x2c[:, 2])
+    assert len(q.environment_atoms()[0]) > 9 * 27
+
+
+def test_rank_layers_cover_the_grid():
+    from critic2_b200 import sharding
+    for nz, lh, world in ((400, 8, 8), (101, 8, 3), (5, 4, 2), (512, 8, 8)):
+        seen = np.zeros(nz, int)
+        for r in range(world):
+            for c0, c1 in sharding.rank_layers(nz, lh, r, world):
+                seen[c0:c1] += 1
+        assert (seen == 1).all()
+        assert sum(sharding.rank_points(nz, lh, r, world, 7) for r in range(world)) == nz * 7
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from critic2_b200 import sharding
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    nz, lh, plane = 21, 4, 6
+    truth = torch.arange(nz * plane, dtype=torch.float64).reshape(nz, plane) * 0.5 + 1.0
+    full = torch.full((nz, plane), 7.0, dtype=torch.float64)     # garbage outside the rank's layers
+    for c0, c1 in sharding.rank_layers(nz, lh, rank, world):
+        full[c0:c1] = truth[c0:c1]                                # "evaluate" own layers
+    sharding.zero_foreign_layers(full, nz, lh, rank, world)
+    sharding.gather_layers(full, nz, lh, rank, world, dist, dst=0)
+    sums = torch.tensor([1.0 + rank, 2.0, 3.0], dtype=torch.float64)
+    sharding.reduce_void_sums(sums, dist)
+    ok = bool(torch.equal(sums, torch.tensor([3.0, 4.0, 6.0], dtype=torch.float64)))
+    if rank == 0:
+        ok = ok and bool(torch.equal(full, truth))
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+def test_two_rank_gather_and_reduction_over_gloo():
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok in res), res

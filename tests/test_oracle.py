@@ -1,0 +1,226 @@
+"""CPU tests that pin the oracle (and the host-side loaders) without the reference binary.
+
+The reference's own CUBE/NCIPLOT regression scripts are absent from the snapshot and no Fortran compiler exists here
+(SURVEY.md 8c), so the pins are known answers:
+  * electron counts 10 / 42 / 18 / 10 from the analytic overlap of the loaded primitive expansion (pins read_fchk /
+    read_wfx normalisation and the spherical->Cartesian tables);
+  * the oracle's rho2 against an independent dense numpy evaluation of the same expansion;
+  * analytic derivatives against Richardson finite differences (the reference's own consistency scheme,
+    fieldmod@proc.f90:932-1127);
+  * single-primitive closed forms, eig against LAPACK, radial tables integrating to Z, interp at nodes.
+"""
+import math
+
+import numpy as np
+import pytest
+
+import cases
+import oracle
+from critic2_b200.wfn import LI
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _build():
+    oracle.build()
+
+
+def _dfact(n):
+    return 1.0 if n <= 0 else float(np.prod(np.arange(n, 0, -2)))
+
+
+def _overlap_1d(l, m, a, b, A, B):
+    """int (x-A)^l (x-B)^m exp(-a(x-A)^2 - b(x-B)^2) dx without the Gaussian-product prefactor; arrays broadcast."""
+    p = a + b
+    P = (a * A + b * B) / p
+    out = np.zeros(np.broadcast(a, b, A, B).shape)
+    for i in range(l + 1):
+        for j in range(m + 1):
+            n = i + j
+            if n % 2:
+                continue
+            mom = _dfact(n - 1) / (2.0 * p) ** (n // 2) * np.sqrt(np.pi / p)
+            out = out + math.comb(l, i) * math.comb(m, j) * (P - A) ** (l - i) * (P - B) ** (m - j) * mom
+    return out
+
+
+def electron_count(f):
+    """sum_mo occ <phi|phi> from the analytic primitive overlap matrix."""
+    ctr = f.xyz[f.icenter - 1]
+    a, b = f.e[:, None], f.e[None, :]
+    S = np.exp(-a * b / (a + b) * ((ctr[:, None, :] - ctr[None, :, :]) ** 2).sum(-1))
+    L = LI[f.itype - 1]
+    for ax in range(3):
+        A, B = ctr[:, ax][:, None], ctr[:, ax][None, :]
+        S1 = np.zeros_like(S)
+        for l in np.unique(L[:, ax]):
+            for m in np.unique(L[:, ax]):
+                sel = (L[:, ax] == l)[:, None] & (L[:, ax] == m)[None, :]
+                if sel.any():
+                    S1 = np.where(sel, _overlap_1d(int(l), int(m), a, b, A, B), S1)
+        S = S * S1
+    C = f.cmo[:, :f.nmoocc]
+    return float(np.einsum("pm,pq,qm,m->", C, S, C, f.occ))
+
+
+@pytest.mark.parametrize("name,nelec", [("h2o-aqz", 10), ("benzene-adz", 42), ("hooh-atz", 18), ("h2o-wfx", 10)])
+def test_electron_count_of_loaded_wavefunctions(name, nelec):
+    f = cases.golden_wfn(name)
+    assert abs(electron_count(f) - nelec) < 2e-5 * nelec
+
+
+def dense_rho(f, r_atoms, pts):
+    """rho, grad by brute force (no screening) in numpy."""
+    ctr = r_atoms[f.icenter - 1]
+    d = pts[:, None, :] - ctr[None, :, :]
+    L = LI[f.itype - 1]
+    ex = np.exp(-f.e[None, :] * (d ** 2).sum(-1))
+    mono = np.prod(d ** L[None, :, :], axis=-1)
+    chi = mono * ex
+    phi = chi @ f.cmo[:, :f.nmoocc]
+    return (phi ** 2) @ f.occ
+
+
+@pytest.mark.parametrize("name", ["h2o-aqz", "hooh-atz", "benzene-adz"])
+def test_rho2_against_dense_numpy(name):
+    f = cases.golden_wfn(name)
+    st = cases.mol_structure(f)
+    rng = np.random.default_rng(1)
+    pts = st.r[rng.integers(0, f.natom, 200)] + rng.normal(0, 1.2, (200, 3))
+    res = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f)).grd_points(pts, nder=0, periodic=False)
+    ref = dense_rho(f, st.r, pts)
+    # the reference screens primitives below 1e-12 of their maximum: agreement to ~1e-10 relative
+    assert np.max(np.abs(res[:, 0] - ref) / ref) < 1e-9
+
+
+def test_derivatives_against_finite_differences():
+    f = cases.golden_wfn("hooh-atz")
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    rng = np.random.default_rng(2)
+    pts = st.r[rng.integers(0, f.natom, 40)] + rng.normal(0, 0.8, (40, 3))
+    res = fld.grd_points(pts, nder=2, periodic=False)
+    h = 1e-4
+    for ax in range(3):
+        e = np.zeros(3)
+        e[ax] = h
+        rp, rm = fld.grd_points(pts + e, 2, False), fld.grd_points(pts - e, 2, False)
+        rp2, rm2 = fld.grd_points(pts + 2 * e, 2, False), fld.grd_points(pts - 2 * e, 2, False)
+        g_fd = (8 * (rp[:, 0] - rm[:, 0]) - (rp2[:, 0] - rm2[:, 0])) / (12 * h)
+        scale = np.abs(res[:, 1:4]).max(1) + res[:, 0]
+        assert np.max(np.abs(g_fd - res[:, 1 + ax]) / scale) < 1e-6
+        # Hessian column from the analytic gradient
+        hcol = (8 * (rp[:, 1:4] - rm[:, 1:4]) - (rp2[:, 1:4] - rm2[:, 1:4])) / (12 * h)
+        ana = res[:, 4:13].reshape(-1, 3, 3)[:, ax, :]   # column-major hf: hf[i + 3j]; symmetric anyway
+        hs = np.abs(res[:, 4:13]).max(1)[:, None] + res[:, [0]]
+        assert np.max(np.abs(hcol - ana) / hs) < 1e-6
+    # gfmod, del2f
+    np.testing.assert_allclose(res[:, 13], np.linalg.norm(res[:, 1:4], axis=1), rtol=1e-14)
+    np.testing.assert_allclose(res[:, 14], res[:, 4] + res[:, 8] + res[:, 12], rtol=1e-13, atol=1e-300)
+
+
+def test_single_primitive_closed_form():
+    """One d_xy Gaussian, one MO: rho = occ c^2 (xy)^2 exp(-2 a r^2) and its gradient."""
+    from critic2_b200.wfn import Molwfn, complete_struct
+    a, c, occ = 0.7, 0.9, 2.0
+    f = Molwfn(natom=1, xyz=np.zeros((1, 3)), z=np.array([6], np.int32), icenter=np.array([1], np.int32),
+               itype=np.array([8], np.int32), e=np.array([a]), occ=np.array([occ]), cmo=np.array([[c]]), nmoocc=1)
+    complete_struct(f)
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    p = np.array([[0.3, -0.4, 0.5], [1.0, 0.2, -0.7]])
+    res = fld.grd_points(st.r[0] + p, 2, False)
+    x, y, z = p.T
+    r2 = x * x + y * y + z * z
+    rho = occ * c * c * (x * y) ** 2 * np.exp(-2 * a * r2)
+    np.testing.assert_allclose(res[:, 0], rho, rtol=1e-13)
+    np.testing.assert_allclose(res[:, 1], rho * (2 / x - 4 * a * x), rtol=1e-12)
+    np.testing.assert_allclose(res[:, 3], rho * (-4 * a * z), rtol=1e-12)
+
+
+def test_nucleus_zeroes_gradient():
+    f = cases.golden_wfn("h2o-aqz")
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    res = fld.grd_points(np.array([st.r[0], st.r[0] + [2e-5, 0, 0]]), 2, True)
+    assert res[0, 15] == 1 and not res[0, 1:4].any() and res[0, 13] == 0
+    assert res[1, 15] == 0 and res[1, 13] > 0
+
+
+def test_eig_against_lapack():
+    rng = np.random.default_rng(5)
+    for _ in range(200):
+        a = rng.normal(size=(3, 3)) * 10 ** rng.uniform(-6, 3)
+        h = a + a.T
+        ev = oracle.eig(h)
+        ref = np.linalg.eigvalsh(h)
+        assert np.max(np.abs(ev - ref)) <= 1e-11 * np.abs(ref).max()
+    assert np.allclose(oracle.eig(np.diag([3.0, -1.0, 2.0])), [-1, 2, 3])
+
+
+@pytest.mark.parametrize("z", [1, 6, 8, 14])
+def test_radial_tables_integrate_to_z(z):
+    t = cases.tables()[z]
+    r, fv = t["r"], t["f"]
+    q = np.trapezoid(4 * np.pi * r ** 3 * fv, np.log(r))   # dr = r dlog r
+    assert abs(q - z) < 2e-3 * z
+    g = oracle.Grid1Set({z: t})
+    k = len(r) // 3
+    f0, fp0, fpp0 = g.interp(z, float(r[k]))
+    assert abs(f0 - fv[k]) <= 1e-12 * abs(fv[k])
+    assert abs(fp0 - t["fp"][k]) <= 1e-10 * abs(t["fp"][k])
+    assert g.interp(z, float(r[-1]) + 1.0) == (0.0, 0.0, 0.0)
+
+
+def test_promolecular_single_atom_and_fd():
+    tabs = cases.tables()
+    from critic2_b200 import structure
+    st = structure.molecular_cell(np.zeros((1, 3)), np.array([8], np.int32))
+    grids = oracle.Grid1Set(tabs)
+    fld = oracle.Field(oracle.Environ(st), grids=grids)
+    p = st.r[0] + np.array([0.6, -0.3, 0.2])
+    res = fld.grd(p, 2, True)
+    rr = np.linalg.norm([0.6, -0.3, 0.2])
+    f0, fp0, _ = grids.interp(8, rr)
+    assert abs(res[0] - f0) < 1e-13 * f0
+    np.testing.assert_allclose(res[1:4], fp0 * np.array([0.6, -0.3, 0.2]) / rr, rtol=1e-12)
+    h = 1e-4
+    for ax in range(3):
+        e = np.zeros(3)
+        e[ax] = h
+        fd = (fld.grd(p + e, 2, True)[0] - fld.grd(p - e, 2, True)[0]) / (2 * h)
+        assert abs(fd - res[1 + ax]) < 1e-5 * np.abs(res[1:4]).max()
+
+
+def test_nci_cutoffs_against_numpy():
+    rng = np.random.default_rng(7)
+    shp = (9, 8, 7)
+    crho = rng.normal(0, 15, shp)
+    cgrad = np.abs(rng.normal(0, 1.5, shp))
+    rhoat = np.abs(rng.normal(0.05, 0.04, shp))
+    cg = cgrad.copy()
+    sums, dat = oracle.nci_cutoffs(crho, cg, rhoat, rhocut=0.2, dimcut=2.0, rhoplot=0.1, srhorange=(-0.08, 0.09),
+                                   onlyneg=False, rho_void=0.06, omega=123.0)
+    inter = rhoat < 0.06
+    n = crho.size
+    np.testing.assert_allclose(sums, [np.abs(crho[inter]).sum() / 100 * 123 / n, rhoat[inter].sum() * 123 / n,
+                                      inter.sum() * 123 / n], rtol=1e-12)
+    isdat = (np.abs(crho) < 20) & (cgrad < 2.0) & inter
+    assert len(dat) == isdat.sum()
+    np.testing.assert_allclose(dat[:, 0], crho[isdat] / 100)
+    mask = (np.abs(crho) > 10) | ~inter | (crho < -8) | (crho > 9)
+    assert np.array_equal(cg == 100.0, mask | (cgrad == 100.0))
+
+
+def test_cube_loop_matches_point_calls_and_layout():
+    f = cases.golden_wfn("h2o-wfx")
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    x0, xd, nn = cases.bbox_grid(st, (5, 4, 3), margin=1.0)
+    c = fld.cube(x0, xd, nn, props=("f", "lap", "hxy"))
+    for (i, j, k) in [(0, 0, 0), (4, 3, 2), (2, 1, 1)]:
+        r = fld.grd(x0 + xd @ np.array([i, j, k], float), 2, False)
+        assert c["f"][k, j, i] == r[0] and c["lap"][k, j, i] == r[14] and c["hxy"][k, j, i] == r[4 + 3]
+    crho, cgrad, _ = fld.nci(x0, xd, nn)
+    assert crho.shape == (5, 4, 3)
+    r = fld.grd(x0 + xd @ np.array([4, 1, 2], float), 2, True)
+    assert abs(abs(crho[4, 1, 2]) - 100 * r[0]) <= 1e-13 * 100 * r[0]
