@@ -6,7 +6,7 @@ Workload (N = any): BASELINE.json configs[3] -- synthetic 500-atom C160N20O20H30
 full pass over the grid; with N GPUs the 50 z-layers of 8 planes are dealt round-robin to the ranks (strong scaling,
 no data-path collective; the gather to the writer rank is part of the e2e leg only).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 400]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--grid 400]
 
 `value`    : points/s, device-resident outputs, CUDA events on the launching stream, max over ranks.
 `e2e`      : the same pass through the C-ABI host entry (c2gpu_eval_grid: host descriptors in, pageable host arrays
@@ -40,10 +40,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=400, help="grid points per axis (400 = the BASELINE config)")
+    ap.add_argument("--grid", dest="n", type=int, default=400, help="grid points per axis (400 = the BASELINE config)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-stride", type=int, default=16, help="sub-lattice stride of the CPU sample")
+    ap.add_argument("--cpu-stride", type=int, default=8, help="sub-lattice stride of the CPU sample")
     return ap.parse_args()
 
 
