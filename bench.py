@@ -263,7 +263,7 @@ def run_ours(a):
                            "kernel": cfg},
                 "roofline": {"bound": "tensor", "achieved": ach, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
                              "frac": ach / FP64_PEAK_TFLOPS, "traffic": None,
-                             "kernel": "wfn_grid_kernel<TileCfg<10,2,7,2,28,1>> (FP64 DMMA)", "kernel_ms": kms,
+                             "kernel": f"wfn_grid_kernel cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, P={cfg['points_per_tile']}, NB={cfg['mo_block']})", "kernel_ms": kms,
                              "algorithmic_flops_per_launch": flops, "mean_n_act": nact / max(mypts, 1),
                              "peak_source": "measured FP64 mma.sync (DMMA) peak, profiles/r1_fp64_peak_microbench.log; "
                                             "MEASURED_PEAKS.json holds no FP64 figure"},

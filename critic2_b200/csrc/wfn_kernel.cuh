@@ -8,7 +8,7 @@
 //   super-tile (e.g. 8x8x8 points)  : S1 ordered warp-ballot compaction of the shells whose screening sphere
 //                                     (dran, :3102-3106) touches the super-tile's bounding box
 //   sub-tile   (P = 8*WM points)    : S2 refine against the sub-tile box, expand to a primitive list
-//   MO block   (NB = 8*NI*WN MOs)   : K loop over chunks of KC active primitives, double buffered:
+//   MO block   (NB = 8*NFRAG MOs)   : K loop over chunks of KC active primitives, double buffered:
 //        A = chi[(d,point) x k]  evaluated in FP64 by all threads into shared memory (exact per-point dran mask)
 //        B = C[k x mo]           gathered row by row with 1-D bulk TMA copies (mbarrier complete_tx)
 //        acc(d,point; mo) += A*B mma.sync m8n8k4 f64; a thread owns all ND derivatives of one point for 2*NI MOs
@@ -33,11 +33,14 @@ struct WfnParams {
   double nci_const;
 };
 
-template <int ND_, int WM_, int WN_, int NI_, int KC_, int CTAS_>
+// NFRAG = 8-column MMA fragments per MO block, dealt to the WN warp columns: warp column wn owns
+// NFRAG/WN (+1 for the first NFRAG%WN columns) consecutive fragments.
+template <int ND_, int WM_, int WN_, int NFRAG_, int KC_, int CTAS_>
 struct TileCfg {
-  static constexpr int ND = ND_, WM = WM_, WN = WN_, NI = NI_, KC = KC_, CTAS = CTAS_;
+  static constexpr int ND = ND_, WM = WM_, WN = WN_, NFRAG = NFRAG_, KC = KC_, CTAS = CTAS_;
+  static constexpr int NI = (NFRAG + WN - 1) / WN;   // most fragments owned by one warp
   static constexpr int P = 8 * WM;            // points per sub-tile
-  static constexpr int NB = 8 * NI * WN;      // MO columns per block
+  static constexpr int NB = 8 * NFRAG;        // MO columns per block
   static constexpr int NT = 32 * WM * WN;     // threads
   static constexpr int NW = WM * WN;
   static constexpr int SLOTS = NT / P;        // primitive slots evaluated concurrently (4*WN)
@@ -80,6 +83,7 @@ __device__ __forceinline__ void block_bbox(double lo[3], double hi[3], double *s
 template <class C>
 __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_constant__ WfnParams p) {
   constexpr int ND = C::ND, P = C::P, NB = C::NB, NT = C::NT, NW = C::NW, WM = C::WM, WN = C::WN, NI = C::NI;
+  constexpr int NFRAG = C::NFRAG;
   constexpr int KC = C::KC, SLOTS = C::SLOTS, R = C::R, SB = C::SB, A_STAGE = C::A_STAGE, B_STAGE = C::B_STAGE;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   double *As = reinterpret_cast<double *>(smem_raw);
@@ -98,6 +102,9 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int wm = warp % WM, wn = warp / WM;
   const int pt = tid % P, slot = tid / P;
+  // fragments of this warp column: [f0, f0 + nfw)
+  const int nfw = NFRAG / WN + (wn < NFRAG % WN ? 1 : 0);
+  const int f0 = wn * (NFRAG / WN) + min(wn, NFRAG % WN);
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
   int *sh_list = p.scratch + (size_t)blockIdx.x * (p.shell_cap + p.prim_cap);
@@ -292,19 +299,20 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
             mbar_wait(&mbar[stg], phase[stg]);
             phase[stg] ^= 1u;
             const double *Ast = As + stg * A_STAGE + (size_t)wm * 32 + aoff;
-            const double *Bst = Bs + stg * B_STAGE + (lane & 3) * SB + wn * (NI * 8) + (lane >> 2);
+            const double *Bst = Bs + stg * B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
             const unsigned char *nzs = s_nz + ((stg * (KC / 4)) * WM + wm) * 32 + lane;
 #pragma unroll 1
             for (int kq = 0; kq < KC / 4; kq++) {
               if (__ballot_sync(~0u, nzs[kq * WM * 32] != 0) == 0u) continue;   // all 8 points x 4 primitives masked
               double b[NI];
 #pragma unroll
-              for (int ni = 0; ni < NI; ni++) b[ni] = Bst[kq * 4 * SB + ni * 8];
+              for (int ni = 0; ni < NI; ni++) b[ni] = (NFRAG % WN == 0 || ni < nfw) ? Bst[kq * 4 * SB + ni * 8] : 0.0;
 #pragma unroll
               for (int d = 0; d < ND; d++) {
                 const double a = Ast[(size_t)(kq * ND + d) * P * 4];
 #pragma unroll
-                for (int ni = 0; ni < NI; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
+                for (int ni = 0; ni < NI; ni++)
+                  if (NFRAG % WN == 0 || ni < nfw) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
               }
             }
             if (c + 1 < nch) chi_phase(c + 1, stg ^ 1);
@@ -317,22 +325,22 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
           for (int ni = 0; ni < NI; ni++)
 #pragma unroll
             for (int j = 0; j < 2; j++) {
-              const double oc = w.occ[blk * NB + wn * (NI * 8) + ni * 8 + 2 * (lane & 3) + j];
-              const double f0 = acc[0][ni][j];
-              q[0] += oc * f0 * f0;
+              const double oc = (NFRAG % WN == 0 || ni < nfw) ? w.occ[blk * NB + (f0 + ni) * 8 + 2 * (lane & 3) + j] : 0.0;
+              const double f0v = acc[0][ni][j];
+              q[0] += oc * f0v * f0v;
               if (ND > 1) {
                 const double t = 2.0 * oc;
                 const double f1 = acc[ND > 1 ? 1 : 0][ni][j], f2 = acc[ND > 1 ? 2 : 0][ni][j], f3 = acc[ND > 1 ? 3 : 0][ni][j];
-                q[ND > 1 ? 1 : 0] += t * f0 * f1;
-                q[ND > 1 ? 2 : 0] += t * f0 * f2;
-                q[ND > 1 ? 3 : 0] += t * f0 * f3;
+                q[ND > 1 ? 1 : 0] += t * f0v * f1;
+                q[ND > 1 ? 2 : 0] += t * f0v * f2;
+                q[ND > 1 ? 3 : 0] += t * f0v * f3;
                 if (ND > 4) {
-                  q[ND > 4 ? 4 : 0] += t * (f0 * acc[ND > 4 ? 4 : 0][ni][j] + f1 * f1);
-                  q[ND > 4 ? 5 : 0] += t * (f0 * acc[ND > 4 ? 5 : 0][ni][j] + f2 * f2);
-                  q[ND > 4 ? 6 : 0] += t * (f0 * acc[ND > 4 ? 6 : 0][ni][j] + f3 * f3);
-                  q[ND > 4 ? 7 : 0] += t * (f0 * acc[ND > 4 ? 7 : 0][ni][j] + f1 * f2);
-                  q[ND > 4 ? 8 : 0] += t * (f0 * acc[ND > 4 ? 8 : 0][ni][j] + f1 * f3);
-                  q[ND > 4 ? 9 : 0] += t * (f0 * acc[ND > 4 ? 9 : 0][ni][j] + f2 * f3);
+                  q[ND > 4 ? 4 : 0] += t * (f0v * acc[ND > 4 ? 4 : 0][ni][j] + f1 * f1);
+                  q[ND > 4 ? 5 : 0] += t * (f0v * acc[ND > 4 ? 5 : 0][ni][j] + f2 * f2);
+                  q[ND > 4 ? 6 : 0] += t * (f0v * acc[ND > 4 ? 6 : 0][ni][j] + f3 * f3);
+                  q[ND > 4 ? 7 : 0] += t * (f0v * acc[ND > 4 ? 7 : 0][ni][j] + f1 * f2);
+                  q[ND > 4 ? 8 : 0] += t * (f0v * acc[ND > 4 ? 8 : 0][ni][j] + f1 * f3);
+                  q[ND > 4 ? 9 : 0] += t * (f0v * acc[ND > 4 ? 9 : 0][ni][j] + f2 * f3);
                 }
               }
             }

@@ -5,13 +5,14 @@ namespace c2 {
 
 long g_launches = 0;
 
-// name, WM, WN, NI, KC, CTAS
+// name, WM, WN, NFRAG, KC, CTAS
 #define C2_WFN_CONFIGS(X) \
   X(0, "S1", 8, 1, 1, 8, 2)   \
   X(1, "S3", 8, 1, 3, 8, 1)   \
-  X(2, "M", 2, 4, 2, 16, 1)   \
-  X(3, "L", 2, 7, 2, 28, 1)   \
-  X(4, "L1", 1, 7, 2, 28, 2)
+  X(2, "M", 2, 4, 8, 16, 1)   \
+  X(3, "L", 2, 7, 14, 28, 1)  \
+  X(4, "L1", 1, 7, 14, 28, 2) \
+  X(5, "L16", 2, 8, 14, 32, 1)
 
 static void tile_shape(int P, int &ta, int &tb, int &tc) {
   switch (P) {
@@ -24,15 +25,15 @@ static void tile_shape(int P, int &ta, int &tb, int &tc) {
 
 static std::vector<WfnCfgInfo> build_infos() {
   std::vector<WfnCfgInfo> v;
-#define X(ID, NAME, WM, WN, NI, KC, CTAS)                                                            \
+#define X(ID, NAME, WM, WN, NF, KC, CTAS)                                                            \
   {                                                                                                  \
     WfnCfgInfo i;                                                                                    \
-    i.name = NAME; i.wm = WM; i.wn = WN; i.ni = NI; i.kc = KC; i.ctas = CTAS;                        \
-    i.P = 8 * WM; i.NB = 8 * NI * WN; i.NT = 32 * WM * WN;                                           \
+    i.name = NAME; i.wm = WM; i.wn = WN; i.ni = NF; i.kc = KC; i.ctas = CTAS;                        \
+    i.P = 8 * WM; i.NB = 8 * NF; i.NT = 32 * WM * WN;                                           \
     tile_shape(i.P, i.ta, i.tb, i.tc);                                                               \
-    i.smem[0] = TileCfg<1, WM, WN, NI, KC, CTAS>::SMEM;                                              \
-    i.smem[1] = TileCfg<4, WM, WN, NI, KC, CTAS>::SMEM;                                              \
-    i.smem[2] = TileCfg<10, WM, WN, NI, KC, CTAS>::SMEM;                                             \
+    i.smem[0] = TileCfg<1, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[1] = TileCfg<4, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[2] = TileCfg<10, WM, WN, NF, KC, CTAS>::SMEM;                                             \
     v.push_back(i);                                                                                  \
   }
   C2_WFN_CONFIGS(X)
@@ -72,11 +73,11 @@ static cudaError_t launch_one(const WfnParams &p, int grid, cudaStream_t st) {
 }
 
 cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st) {
-#define X(ID, NAME, WM, WN, NI, KC, CTAS)                                          \
+#define X(ID, NAME, WM, WN, NF, KC, CTAS)                                          \
   if (cfg == ID) {                                                                 \
-    if (nd == 1) return launch_one<TileCfg<1, WM, WN, NI, KC, CTAS>>(p, grid, st); \
-    if (nd == 4) return launch_one<TileCfg<4, WM, WN, NI, KC, CTAS>>(p, grid, st); \
-    return launch_one<TileCfg<10, WM, WN, NI, KC, CTAS>>(p, grid, st);             \
+    if (nd == 1) return launch_one<TileCfg<1, WM, WN, NF, KC, CTAS>>(p, grid, st); \
+    if (nd == 4) return launch_one<TileCfg<4, WM, WN, NF, KC, CTAS>>(p, grid, st); \
+    return launch_one<TileCfg<10, WM, WN, NF, KC, CTAS>>(p, grid, st);             \
   }
   C2_WFN_CONFIGS(X)
 #undef X
