@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--grid", dest="n", type=int, default=400, help="grid points per axis (400 = the BASELINE config)")
+    ap.add_argument("--cfg", type=int, default=-1, help="force a wavefunction kernel configuration (development)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-stride", type=int, default=8, help="sub-lattice stride of the CPU sample")
@@ -159,6 +160,8 @@ def run_ours(a):
     dev = torch.device("cuda", local)
 
     f, st, lo, xd, nn = workload(a.n)
+    if a.cfg >= 0:
+        gpu.set_option("wfn_cfg", a.cfg)
     fld = gpu.WfnField(f, st)
     cfg = fld.config()
     npts_total = int(nn[0]) * int(nn[1]) * int(nn[2])

@@ -66,6 +66,9 @@ struct Replica {
   PromolDev m{};
   int *scratch = nullptr, *counter = nullptr;
   int grid = 0;
+  double *acache = nullptr;   // warp-specialised kernel: chi-tile cache (see WfnParams)
+  int *acache_nz = nullptr;
+  int acache_chunks = 0;
 };
 
 struct Handle {
@@ -251,10 +254,16 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     rc |= upload(r, edf_cc, &w.edf_cc);
     rc |= upload(r, edf_l, &w.edf_l);
     r.grid = r.nsm * ci.ctas;
-    size_t per_cta = (size_t)h->nshell + (size_t)npri + 64;
+    size_t per_cta = (size_t)(h->nshell + (h->nshell & 1)) + 2 * ((size_t)npri + 64);
     void *d = nullptr;
     if (!rc && cudaMalloc(&d, sizeof(int) * per_cta * r.grid) == cudaSuccess) { r.allocs.push_back(d); r.scratch = (int *)d; } else rc = 2;
     if (!rc && cudaMalloc(&d, 64) == cudaSuccess) { r.allocs.push_back(d); r.counter = (int *)d; } else rc = 2;
+    if (!rc && h->cfg == 6) {
+      r.acache_chunks = std::min((npri + 31) / 32, 128);
+      size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
+      if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
+      if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;
+    }
     if (!rc && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) rc = 2;
     if (rc) {
       std::string msg = g_err.empty() ? "device allocation failed" : g_err;

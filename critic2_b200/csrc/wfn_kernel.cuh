@@ -31,6 +31,10 @@ struct WfnParams {
   int *scratch;         // per CTA: shell list [shell_cap] then primitive list [prim_cap]
   int shell_cap, prim_cap;
   double nci_const;
+  // warp-specialised kernel only: per-CTA cache of chi tiles in global memory (L2), re-used by MO blocks 1..nblk-1
+  double *acache;       // [grid][2 tile parities][acache_chunks][A_STAGE]
+  int *acache_nz;       // [grid][2][acache_chunks][8] k-quad masks
+  int acache_chunks;
 };
 
 // NFRAG = 8-column MMA fragments per MO block, dealt to the WN warp columns: warp column wn owns

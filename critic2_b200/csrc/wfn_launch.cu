@@ -1,5 +1,6 @@
 // wfn_launch.cu -- instantiations and launch dispatch of the wavefunction grid kernel (sm_100a).
 #include "c2gpu_internal.h"
+#include "wfn_ws_kernel.cuh"
 
 namespace c2 {
 
@@ -38,6 +39,14 @@ static std::vector<WfnCfgInfo> build_infos() {
   }
   C2_WFN_CONFIGS(X)
 #undef X
+  {  // id 6: warp-specialised producer/consumer kernel (wfn_ws_kernel.cuh)
+    WfnCfgInfo i;
+    i.name = "WS"; i.wm = 2; i.wn = 4; i.ni = 14; i.kc = WsCfg<10>::KC; i.ctas = 1;
+    i.P = 16; i.NB = 112; i.NT = WsCfg<10>::NT;
+    tile_shape(i.P, i.ta, i.tb, i.tc);
+    i.smem[0] = WsCfg<1>::SMEM; i.smem[1] = WsCfg<4>::SMEM; i.smem[2] = WsCfg<10>::SMEM;
+    v.push_back(i);
+  }
   return v;
 }
 
@@ -72,7 +81,27 @@ static cudaError_t launch_one(const WfnParams &p, int grid, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+template <class C>
+static cudaError_t launch_ws(const WfnParams &p, int grid, cudaStream_t st) {
+  static bool attr_set[16] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 16 && !attr_set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(wfn_ws_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  wfn_ws_kernel<C><<<grid, C::NT, C::SMEM, st>>>(p);
+  g_launches++;
+  return cudaGetLastError();
+}
+
 cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st) {
+  if (cfg == 6) {
+    if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);
+    if (nd == 4) return launch_ws<WsCfg<4>>(p, grid, st);
+    return launch_ws<WsCfg<10>>(p, grid, st);
+  }
 #define X(ID, NAME, WM, WN, NF, KC, CTAS)                                          \
   if (cfg == ID) {                                                                 \
     if (nd == 1) return launch_one<TileCfg<1, WM, WN, NF, KC, CTAS>>(p, grid, st); \
