@@ -254,7 +254,7 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     rc |= upload(r, edf_cc, &w.edf_cc);
     rc |= upload(r, edf_l, &w.edf_l);
     r.grid = r.nsm * ci.ctas;
-    size_t per_cta = (size_t)(h->nshell + (h->nshell & 1)) + 2 * ((size_t)npri + 64);
+    size_t per_cta = (size_t)((h->nshell + 3) & ~3) + 2 * ((size_t)((npri + 1) & ~1) + 64);
     void *d = nullptr;
     if (!rc && cudaMalloc(&d, sizeof(int) * per_cta * r.grid) == cudaSuccess) { r.allocs.push_back(d); r.scratch = (int *)d; } else rc = 2;
     if (!rc && cudaMalloc(&d, 64) == cudaSuccess) { r.allocs.push_back(d); r.counter = (int *)d; } else rc = 2;

@@ -421,6 +421,7 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
         }
         emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs, isnuc, p.nci_const);
       }
+      __syncthreads();   // the epilogue threads are done with s_tot / s_pt before the next sub-tile overwrites them
     }
   }
 }

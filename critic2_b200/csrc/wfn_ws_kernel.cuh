@@ -7,7 +7,7 @@
 //     screening (S1/S2), the chi tiles (A operand) and the bulk-TMA gather of C rows (B operand);
 //   * 8 CONSUMER warps (two per sub-partition, 4+3 MMA fragments each so that every sub-partition carries 7 of the
 //     14 fragments of a 112-column MO block) only wait on mbarriers, issue DMMAs and run the fused epilogue;
-//   * registers are re-balanced with setmaxnreg (consumers 216, producers 72): the consumers hold 10x4x2 accumulators;
+//   * registers are re-balanced with setmaxnreg (consumers 208, producers 88): the consumers hold 10x4x2 accumulators;
 //   * stages hand over through full/empty mbarriers (no block-wide barrier in steady state), and the stream of
 //     (sub-tile, MO block, chunk) steps is continuous, so producers run ahead across block and tile boundaries.
 #pragma once
@@ -31,7 +31,7 @@ struct WsCfg {
   static constexpr int TSLOTS = 4;              // tile-info ring (>= NS + 1)
   static constexpr int NPART = 2 * 4 * P * ND;  // s_part doubles: [2][4 warp columns][P][ND]
   static constexpr size_t SMEM = sizeof(double) * (NS * (A_STAGE + B_STAGE) + NPART + P * ND + TSLOTS * 4 * P) + 256;
-  static constexpr int REG_CONS = 216, REG_PROD = 72;
+  static constexpr int REG_CONS = 208, REG_PROD = 88;
 };
 
 // Per-stage header written by the producers, read by the consumers.
@@ -304,6 +304,10 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
             int prev_sh = -1;
             double dx = 0, dy = 0, dz = 0, ex = 0, al = 0;
             bool pass = false;
+            // the quad's four (primitive, shell) pairs in one 32-byte load (prim_cap is padded, entries past kact unused)
+            const int4 pa = reinterpret_cast<const int4 *>(pr_list + c * KC + grp * 4)[0];
+            const int4 pb4 = reinterpret_cast<const int4 *>(pr_list + c * KC + grp * 4)[1];
+            const int2 psq[4] = {make_int2(pa.x, pa.y), make_int2(pa.z, pa.w), make_int2(pb4.x, pb4.y), make_int2(pb4.z, pb4.w)};
 #pragma unroll
             for (int k4 = 0; k4 < 4; k4++) {
               const int gk = c * KC + grp * 4 + k4;
@@ -311,7 +315,7 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
 #pragma unroll
               for (int d = 0; d < ND; d++) chi[d] = 0.0;
               if (gk < kact && pvalid) {
-                const int2 ps = pr_list[gk];
+                const int2 ps = psq[k4];
                 if (ps.y != prev_sh) {   // new shell: distance screen (:2747) and exponential (:2749) shared by its primitives
                   prev_sh = ps.y;
                   const double4 xa = w.shell_xa[ps.y];
@@ -363,6 +367,26 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
 // ---------------------------------------------------------------------------------------------------------------
 // Consumer side: 256 threads, named barrier 1
 // ---------------------------------------------------------------------------------------------------------------
+// MMAs of one stage for a consumer warp that owns NF fragments (8-column groups) of the MO block.
+template <class C, int NF>
+__device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][C::NI][2], const double *Ast, const double *Bst,
+                                             const int *nzmask, int wm) {
+  constexpr int ND = C::ND, P = C::P, SB = C::SB;
+#pragma unroll 1
+  for (int kq = 0; kq < C::NKQ; kq++) {
+    if (!((nzmask[kq] >> wm) & 1)) continue;             // all 8 points x 4 primitives masked (warp-uniform)
+    double b[NF];
+#pragma unroll
+    for (int ni = 0; ni < NF; ni++) b[ni] = Bst[kq * 4 * SB + ni * 8];
+#pragma unroll
+    for (int d = 0; d < ND; d++) {
+      const double a = Ast[(size_t)(kq * ND + d) * P * 4];
+#pragma unroll
+      for (int ni = 0; ni < NF; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
+    }
+  }
+}
+
 template <class C>
 __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) {
   constexpr int ND = C::ND, P = C::P, NS = C::NS, NB = C::NB, SB = C::SB, NI = C::NI, NCT = C::NCT, NKQ = C::NKQ;
@@ -389,20 +413,9 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     if (!(flags & 8)) {
       const double *Ast = S.As + stg * C::A_STAGE + (size_t)wm * 32 + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
-#pragma unroll 1
-      for (int kq = 0; kq < NKQ; kq++) {
-        if (!((h.nzmask[kq] >> wm) & 1)) continue;       // all 8 points x 4 primitives masked (warp-uniform)
-        double b[NI];
-#pragma unroll
-        for (int ni = 0; ni < NI; ni++) b[ni] = (ni < 3 || nfw == 4) ? Bst[kq * 4 * SB + ni * 8] : 0.0;
-#pragma unroll
-        for (int d = 0; d < ND; d++) {
-          const double a = Ast[(size_t)(kq * ND + d) * P * 4];
-#pragma unroll
-          for (int ni = 0; ni < NI; ni++)
-            if (ni < 3 || nfw == 4) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
-        }
-      }
+      // warp-uniform choice of the fragment count: a predicated-off DMMA still occupies the tensor pipe
+      if (nfw == 4) ws_mma_stage<C, 4>(acc, Ast, Bst, h.nzmask, wm);
+      else ws_mma_stage<C, 3>(acc, Ast, Bst, h.nzmask, wm);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&S.empty[stg]);           // stage (and its header) no longer needed by this warp
