@@ -68,6 +68,7 @@ struct Replica {
   int grid = 0;
   double *acache = nullptr;   // warp-specialised kernel: chi-tile cache (see WfnParams)
   int *acache_nz = nullptr;
+  double *ws_rec = nullptr;
   int acache_chunks = 0;
 };
 
@@ -263,6 +264,8 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
       size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
       if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
       if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;
+      size_t prim_cap = (size_t)((npri + 1) & ~1) + 64;
+      if (!rc && cudaMalloc(&d, (size_t)r.grid * prim_cap * 64) == cudaSuccess) { r.allocs.push_back(d); r.ws_rec = (double *)d; } else rc = 2;
     }
     if (!rc && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) rc = 2;
     if (rc) {

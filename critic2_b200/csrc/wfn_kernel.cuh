@@ -34,6 +34,7 @@ struct WfnParams {
   // warp-specialised kernel only: per-CTA cache of chi tiles in global memory (L2), re-used by MO blocks 1..nblk-1
   double *acache;       // [grid][2 tile parities][acache_chunks][A_STAGE]
   int *acache_nz;       // [grid][2][acache_chunks][8] k-quad masks
+  double *ws_rec;       // [grid][prim_cap][8] records of the active primitives of the current sub-tile
   int acache_chunks;
 };
 

@@ -63,7 +63,7 @@ int wfn_choose_config(int nmo, int force) {
   if (nfrag <= 1) return 0;
   if (nfrag <= 3) return 1;
   int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
-  return (padM < padL) ? 2 : 3;
+  return (padM < padL) ? 2 : 6;
 }
 
 template <class C>

@@ -24,7 +24,7 @@ struct WsCfg {
   static constexpr int NT = 32 * (NCW + NPW);
   static constexpr int NCT = 32 * NCW, NPT = 32 * NPW;
   static constexpr int KC = 32, NKQ = KC / 4;   // primitives per stage
-  static constexpr int NS = 2;                  // stages
+  static constexpr int NS = 3;                  // stages
   static constexpr int NI = 4;                  // most fragments per consumer warp
   static constexpr int SB = 116;                // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
@@ -108,6 +108,9 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
   // per-CTA scratch: shell list [shell_cap, even] then (primitive, shell) pairs [prim_cap]
   int *sh_list = p.scratch + (size_t)blockIdx.x * (p.shell_cap + 2 * p.prim_cap);
   int2 *pr_list = reinterpret_cast<int2 *>(sh_list + p.shell_cap);
+  // 64-byte records of the active primitives of the current sub-tile: x, y, z, alpha, dran, dran^2, bits, 0 with
+  // bits = shell id | lx << 32 | ly << 40 | lz << 48 (everything the chi evaluation needs: one coalesced load per quad)
+  double *rec = p.ws_rec + (size_t)blockIdx.x * (size_t)p.prim_cap * 8;
   const int na = grid_na(g), nb = grid_nb(g);
   const int npsuper = g.sa * g.sb * g.sc;
   const int nsub_a = g.sa / g.ta, nsub_b = g.sb / g.tb, nsub_c = g.sc / g.tc;
@@ -238,7 +241,18 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
           tot += S.p_cnt[i];
         }
         off += incl - cnt;
-        for (int i = 0; i < cnt; i++) pr_list[off + i] = make_int2(pb + i, s);
+        if (cnt > 0) {
+          const double4 xa = w.shell_xa[s];
+          const double2 cut = w.shell_cut[s];
+          for (int i = 0; i < cnt; i++) {
+            pr_list[off + i] = make_int2(pb + i, s);
+            const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[pb + i];
+            const long long bits = (long long)s | ((long long)l.x << 32) | ((long long)l.y << 40) | ((long long)l.z << 48);
+            double4 *r = reinterpret_cast<double4 *>(rec + (size_t)(off + i) * 8);
+            r[0] = xa;
+            r[1] = make_double4(cut.x, cut.y, __longlong_as_double(bits), 0.0);
+          }
+        }
         kact += tot;
         named_bar_sync(2, NPT);
       }
@@ -258,14 +272,19 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
         publish(stg);
         continue;
       }
+      auto load_rec = [&](int cc) -> double2 {
+        return reinterpret_cast<const double2 *>(rec + (size_t)(cc * KC + grp * 4) * 8)[pt];
+      };
+      double2 rec_next = make_double2(0.0, 0.0);
       double *agbase = p.acache + ((size_t)blockIdx.x * 2 + (tcount & 1)) * (size_t)p.acache_chunks * C::A_STAGE;
       int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + (tcount & 1)) * (size_t)p.acache_chunks * 8;
       for (int blk = 0; blk < p.nblk; blk++) {
-        if (blk == 1) {   // chi tiles written by every producer thread -> visible to the bulk-TMA reads below
+        if (blk == 1) {   // bulk stores of the chi tiles complete, k-quad masks visible -> safe to read them back
+          if (ptid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
           __threadfence();
-          asm volatile("fence.proxy.async;" ::: "memory");
           named_bar_sync(2, NPT);
         }
+        if (blk == 0 || nch > p.acache_chunks) rec_next = load_rec(blk == 0 ? 0 : p.acache_chunks);
         for (int c = 0; c < nch; c++) {
           const int stg = acquire();
           const bool cached = c < p.acache_chunks;           // this chunk's chi tile lives in the L2 cache
@@ -296,49 +315,47 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
             }
           }
           if (compute) {
-            // A tile: this 16-lane group evaluates the 4 primitives of k-quad `grp` at its 16 points
+            // A tile: this 16-lane group evaluates the 4 primitives of k-quad `grp` at its 16 points.  The quad's four
+            // records (256 contiguous bytes) were loaded one chunk ahead, 16 bytes per lane, and are passed round
+            // with shuffles: no dependent global load sits between acquiring the stage and the arithmetic.
+            const double2 mine = rec_next;
+            if (c + 1 < nch) rec_next = load_rec(c + 1);
             const size_t aoffq = (size_t)(grp * ND) * P * 4 + pt * 4;
             double *Aq = S.As + stg * C::A_STAGE + aoffq;
-            double *Ag = agbase + (size_t)c * C::A_STAGE + aoffq;
             unsigned nzbits = 0;
             int prev_sh = -1;
             double dx = 0, dy = 0, dz = 0, ex = 0, al = 0;
             bool pass = false;
-            // the quad's four (primitive, shell) pairs in one 32-byte load (prim_cap is padded, entries past kact unused)
-            const int4 pa = reinterpret_cast<const int4 *>(pr_list + c * KC + grp * 4)[0];
-            const int4 pb4 = reinterpret_cast<const int4 *>(pr_list + c * KC + grp * 4)[1];
-            const int2 psq[4] = {make_int2(pa.x, pa.y), make_int2(pa.z, pa.w), make_int2(pb4.x, pb4.y), make_int2(pb4.z, pb4.w)};
+            const int sbase = lane & 16;
 #pragma unroll
             for (int k4 = 0; k4 < 4; k4++) {
               const int gk = c * KC + grp * 4 + k4;
+              const double rx = __shfl_sync(~0u, mine.x, sbase + k4 * 4), ry = __shfl_sync(~0u, mine.y, sbase + k4 * 4);
+              const double rz = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 1), ra = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 1);
+              const double rc = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 2), rc2 = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 2);
+              const long long bits = __double_as_longlong(__shfl_sync(~0u, mine.x, sbase + k4 * 4 + 3));
               double chi[ND];
 #pragma unroll
               for (int d = 0; d < ND; d++) chi[d] = 0.0;
               if (gk < kact && pvalid) {
-                const int2 ps = psq[k4];
-                if (ps.y != prev_sh) {   // new shell: distance screen (:2747) and exponential (:2749) shared by its primitives
-                  prev_sh = ps.y;
-                  const double4 xa = w.shell_xa[ps.y];
-                  const double2 cut = w.shell_cut[ps.y];
-                  dx = px - xa.x; dy = py - xa.y; dz = pz - xa.z;
-                  al = xa.w;
+                const int sh = (int)(bits & 0xffffffffll);
+                if (sh != prev_sh) {   // new shell: distance screen (:2747) and exponential (:2749) shared by its primitives
+                  prev_sh = sh;
+                  dx = px - rx; dy = py - ry; dz = pz - rz;
+                  al = ra;
                   const double d2 = dx * dx + dy * dy + dz * dz;
-                  pass = within_cut(dx, dy, dz, d2, cut.x, cut.y);
+                  pass = within_cut(dx, dy, dz, d2, rc, rc2);
                   ex = pass ? exp(-al * d2) : 0.0;
                 }
                 if (pass) {
-                  const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[ps.x];
-                  prim_chi<ND>(dx, dy, dz, l.x, l.y, l.z, al, ex, chi);
+                  prim_chi<ND>(dx, dy, dz, (int)((bits >> 32) & 0xff), (int)((bits >> 40) & 0xff), (int)((bits >> 48) & 0xff),
+                               al, ex, chi);
                   nzbits |= 1u;
                 }
               }
               const int sw = k4 ^ ((pt >> 2) & 3);
 #pragma unroll
               for (int d = 0; d < ND; d++) Aq[d * P * 4 + sw] = chi[d];
-              if (save) {
-#pragma unroll
-                for (int d = 0; d < ND; d++) Ag[d * P * 4 + sw] = chi[d];
-              }
             }
             // k-quad mask: bit wm set if any of the 8 points of row group wm has an unmasked primitive in this quad
             const unsigned bal = __ballot_sync(~0u, nzbits != 0);
@@ -347,6 +364,18 @@ __device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) 
               const int m = ((half & 0xffu) ? 1 : 0) | ((half & 0xff00u) ? 2 : 0);
               S.hdr[stg].nzmask[grp] = m;
               if (save) nzbase[c * 8 + grp] = m;
+            }
+            if (save) {
+              // copy the finished tile to the L2 cache with one bulk TMA store (shared -> global)
+              fence_proxy_async();
+              named_bar_sync(2, NPT);
+              if (ptid == 0) {
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous store has read its stage
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(agbase + (size_t)c * C::A_STAGE),
+                             "r"(smem_u32(S.As + stg * C::A_STAGE)), "r"((uint32_t)(C::A_STAGE * sizeof(double)))
+                             : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              }
             }
           }
           publish(stg);
