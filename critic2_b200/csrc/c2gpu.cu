@@ -184,6 +184,8 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
   set_cell(h->xf, ismolecule, m_x2c, m_c2x, nullptr, nullptr);
   h->natom = natom; h->npri = npri; h->nmo = nmoocc;
   h->cfg = wfn_choose_config(nmoocc, g_force_cfg);
+  // the split-producer kernel keeps every chi tile of a sub-tile in its cache: 80 KB per 32 primitives and CTA
+  if (h->cfg == 7 && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 6;
   const WfnCfgInfo &ci = wfn_cfg_info(h->cfg);
   h->nblk = (nmoocc + ci.NB - 1) / ci.NB;
   const int ldc = h->nblk * ci.NB;
@@ -255,12 +257,13 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     rc |= upload(r, edf_cc, &w.edf_cc);
     rc |= upload(r, edf_l, &w.edf_l);
     r.grid = r.nsm * ci.ctas;
-    size_t per_cta = (size_t)((h->nshell + 3) & ~3) + 2 * ((size_t)((npri + 1) & ~1) + 64);
+    size_t per_cta = (size_t)((h->nshell + 3) & ~3) + 4 * ((size_t)((npri + 1) & ~1) + 64);
     void *d = nullptr;
     if (!rc && cudaMalloc(&d, sizeof(int) * per_cta * r.grid) == cudaSuccess) { r.allocs.push_back(d); r.scratch = (int *)d; } else rc = 2;
     if (!rc && cudaMalloc(&d, 64) == cudaSuccess) { r.allocs.push_back(d); r.counter = (int *)d; } else rc = 2;
-    if (!rc && h->cfg == 6) {
-      r.acache_chunks = std::min((npri + 31) / 32, 128);
+    if (!rc && h->cfg >= 6) {
+      // cfg 6 caches the first 128 chunks of a sub-tile and recomputes the rest; cfg 7 (split producer) caches all
+      r.acache_chunks = h->cfg == 6 ? std::min((npri + 31) / 32, 128) : (npri + 31) / 32;
       size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
       if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
       if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;
