@@ -185,7 +185,7 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
   h->natom = natom; h->npri = npri; h->nmo = nmoocc;
   h->cfg = wfn_choose_config(nmoocc, g_force_cfg);
   // the split-producer kernel keeps every chi tile of a sub-tile in its cache: 80 KB per 32 primitives and CTA
-  if (h->cfg == 7 && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 6;
+  if (h->cfg == 6 && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 3;
   const WfnCfgInfo &ci = wfn_cfg_info(h->cfg);
   h->nblk = (nmoocc + ci.NB - 1) / ci.NB;
   const int ldc = h->nblk * ci.NB;
@@ -262,8 +262,7 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     if (!rc && cudaMalloc(&d, sizeof(int) * per_cta * r.grid) == cudaSuccess) { r.allocs.push_back(d); r.scratch = (int *)d; } else rc = 2;
     if (!rc && cudaMalloc(&d, 64) == cudaSuccess) { r.allocs.push_back(d); r.counter = (int *)d; } else rc = 2;
     if (!rc && h->cfg >= 6) {
-      // cfg 6 caches the first 128 chunks of a sub-tile and recomputes the rest; cfg 7 (split producer) caches all
-      r.acache_chunks = h->cfg == 6 ? std::min((npri + 31) / 32, 128) : (npri + 31) / 32;
+      r.acache_chunks = (npri + 31) / 32;   // worst case: every primitive active in a sub-tile
       size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
       if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
       if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;

@@ -46,8 +46,6 @@ static std::vector<WfnCfgInfo> build_infos() {
     tile_shape(i.P, i.ta, i.tb, i.tc);
     i.smem[0] = WsCfg<1>::SMEM; i.smem[1] = WsCfg<4>::SMEM; i.smem[2] = WsCfg<10>::SMEM;
     v.push_back(i);
-    i.name = "WG";  // id 7: same consumers, split producer (generator warps one sub-tile ahead + TMA streamer warp)
-    v.push_back(i);
   }
   return v;
 }
@@ -65,7 +63,7 @@ int wfn_choose_config(int nmo, int force) {
   if (nfrag <= 1) return 0;
   if (nfrag <= 3) return 1;
   int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
-  return (padM < padL) ? 2 : 7;
+  return (padM < padL) ? 2 : 6;
 }
 
 template <class C>
@@ -83,31 +81,26 @@ static cudaError_t launch_one(const WfnParams &p, int grid, cudaStream_t st) {
   return cudaGetLastError();
 }
 
-template <class C, bool SPLIT>
+template <class C>
 static cudaError_t launch_ws(const WfnParams &p, int grid, cudaStream_t st) {
   static bool attr_set[16] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 16 && !attr_set[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(wfn_ws_kernel<C, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+    cudaError_t e = cudaFuncSetAttribute(wfn_ws_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  wfn_ws_kernel<C, SPLIT><<<grid, C::NT, C::SMEM, st>>>(p);
+  wfn_ws_kernel<C><<<grid, C::NT, C::SMEM, st>>>(p);
   g_launches++;
   return cudaGetLastError();
 }
 
 cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st) {
   if (cfg == 6) {
-    if (nd == 1) return launch_ws<WsCfg<1>, false>(p, grid, st);
-    if (nd == 4) return launch_ws<WsCfg<4>, false>(p, grid, st);
-    return launch_ws<WsCfg<10>, false>(p, grid, st);
-  }
-  if (cfg == 7) {
-    if (nd == 1) return launch_ws<WsCfg<1>, true>(p, grid, st);
-    if (nd == 4) return launch_ws<WsCfg<4>, true>(p, grid, st);
-    return launch_ws<WsCfg<10>, true>(p, grid, st);
+    if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);
+    if (nd == 4) return launch_ws<WsCfg<4>>(p, grid, st);
+    return launch_ws<WsCfg<10>>(p, grid, st);
   }
 #define X(ID, NAME, WM, WN, NF, KC, CTAS)                                          \
   if (cfg == ID) {                                                                 \

@@ -29,9 +29,9 @@ struct WsCfg {
   static constexpr int SB = 116;                // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
   static constexpr int TSLOTS = 8;              // tile-info ring (>= NS + 3, see ws_generator)
-  static constexpr int NPART = 2 * 4 * P * ND;  // s_part doubles: [2][4 warp columns][P][ND]
-  static constexpr size_t SMEM = sizeof(double) * (NS * (A_STAGE + B_STAGE) + NPART + P * ND + TSLOTS * 4 * P) + 256;
-  static constexpr int REG_CONS = 208, REG_PROD = 88;
+  static constexpr int NPART = 2 * 4 * P * ND;  // s_part doubles: [2 sub-tile parities][4 warp columns][P][ND]
+  static constexpr size_t SMEM = sizeof(double) * (NS * (A_STAGE + B_STAGE) + NPART + TSLOTS * 4 * P) + 256;
+  static constexpr int REG_CONS4 = 232, REG_CONS3 = 184, REG_PROD = 88;   // per warpgroup (setmaxnreg)
 };
 
 // Per-stage header written by the producers, read by the consumers.
@@ -40,7 +40,7 @@ struct WsStageHdr {
                  // bit3 no data (sub-tile without active primitives), bit4 exit
   int blk;       // MO block
   int tslot;     // tile-info slot of the sub-tile
-  int nzmask[WsCfg<1>::NKQ];   // per k-quad: bit wm set if any of the 8 points x 4 primitives is unmasked
+  int kqmask[2];   // per 8-point row group wm: bit kq set if k-quad kq has an unmasked (point, primitive) pair
 };
 struct WsTileInfo {
   int a0, b0, c0;   // sub-tile origin in output coordinates
@@ -70,7 +70,7 @@ __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.al
 // ---------------------------------------------------------------------------------------------------------------
 template <class C>
 struct WsShared {
-  double *As, *Bs, *s_part, *s_tot, *s_pt;   // s_pt: [TSLOTS][4][P] (x,y,z,valid)
+  double *As, *Bs, *s_part, *s_pt;           // s_pt: [TSLOTS][4][P] (x,y,z,valid)
   uint64_t *full, *empty;                    // [NS]
   WsStageHdr *hdr;                           // [NS]
   WsTileInfo *tinfo;                         // [TSLOTS]
@@ -104,306 +104,11 @@ __device__ __forceinline__ void ws_prod_bbox(double lo[3], double hi[3], const W
   named_bar_sync(2, NW * 32);
 }
 
-template <class C>
-__device__ void ws_producer(const WfnParams &p, const WsShared<C> &S, int ptid) {
-  constexpr int ND = C::ND, P = C::P, KC = C::KC, NS = C::NS, NB = C::NB, SB = C::SB, NPT = C::NPT, NPW = C::NPW;
-  const int lane = ptid & 31, warp = ptid >> 5;
-  const int grp = ptid >> 4;        // 8 groups of 16 lanes: group = k-quad of the stage
-  const int pt = ptid & 15;         // point of the sub-tile
-  const WfnDev &w = p.w;
-  const GridDesc &g = p.g;
-  // per-CTA scratch: shell list [shell_cap, even] then (primitive, shell) pairs [prim_cap]
-  int *sh_list = p.scratch + (size_t)blockIdx.x * (p.shell_cap + 2 * p.prim_cap);
-  int2 *pr_list = reinterpret_cast<int2 *>(sh_list + p.shell_cap);
-  // 64-byte records of the active primitives of the current sub-tile: x, y, z, alpha, dran, dran^2, bits, 0 with
-  // bits = shell id | lx << 32 | ly << 40 | lz << 48 (everything the chi evaluation needs: one coalesced load per quad)
-  double *rec = p.ws_rec + (size_t)blockIdx.x * (size_t)p.prim_cap * 8;
-  const int na = grid_na(g), nb = grid_nb(g);
-  const int npsuper = g.sa * g.sb * g.sc;
-  const int nsub_a = g.sa / g.ta, nsub_b = g.sb / g.tb, nsub_c = g.sc / g.tc;
-  unsigned it = 0;                  // stage counter (stage = it % NS, phase = (it / NS) & 1)
-  unsigned tcount = 0;              // sub-tile counter (tile slot = tcount % TSLOTS)
-
-  // acquire the next stage (wait until the consumers released it)
-  auto acquire = [&]() -> int {
-    const int stg = it % NS;
-    mbar_wait(&S.empty[stg], ((it / NS) & 1u) ^ 1u);
-    return stg;
-  };
-  auto publish = [&](int stg) {
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&S.full[stg]);
-    it++;
-  };
-
-  for (;;) {
-    if (ptid == 0) S.p_int[0] = atomicAdd(p.work_counter, 1);
-    named_bar_sync(2, NPT);
-    const int st = S.p_int[0];
-    if (st >= p.nsa * p.nsb * p.nsc) break;
-    const int sa0 = (st % p.nsa) * g.sa, sb0 = ((st / p.nsa) % p.nsb) * g.sb;
-    const int sc0 = g.c0 + (g.c_part + (st / (p.nsa * p.nsb)) * g.c_nparts) * g.sc;
-    // ---- S1: super-tile box, ordered shell compaction, nucleus candidates ---------------------------------------
-    {
-      double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-      for (int q = ptid; q < npsuper; q += NPT) {
-        int a = sa0 + q % g.sa, b = sb0 + (q / g.sa) % g.sb, c = sc0 + q / (g.sa * g.sb);
-        if (a < na && b < nb && c < g.c1) {
-          double x[3], wc[3], wcr[3];
-          grid_point(g, a, b, c, x);
-          grd_wrap(p.xf, x, g.periodic, wc, wcr);
-#pragma unroll
-          for (int d = 0; d < 3; d++) { lo[d] = fmin(lo[d], wcr[d]); hi[d] = fmax(hi[d], wcr[d]); }
-        }
-      }
-      ws_prod_bbox<C>(lo, hi, S, S.p_bb, ptid);
-    }
-    if (ptid == 0) S.p_int[1] = 0;
-    named_bar_sync(2, NPT);
-    int ns = 0;
-    for (int base = 0; base < w.nshell; base += NPT) {
-      int s = base + ptid;
-      bool act = false;
-      if (s < w.nshell) {
-        double4 xa = w.shell_xa[s];
-        act = box_d2(S.p_bb, xa.x, xa.y, xa.z) <= w.shell_cut[s].y * (1.0 + 1e-12);
-      }
-      unsigned m = __ballot_sync(~0u, act);
-      if (lane == 0) S.p_cnt[warp] = __popc(m);
-      named_bar_sync(2, NPT);
-      int off = ns, tot = 0;
-#pragma unroll
-      for (int i = 0; i < NPW; i++) {
-        if (i < warp) off += S.p_cnt[i];
-        tot += S.p_cnt[i];
-      }
-      if (act) sh_list[off + __popc(m & ((1u << lane) - 1u))] = s;
-      ns += tot;
-      named_bar_sync(2, NPT);
-    }
-    __shared__ int s_nuc_tmp[16];
-    for (int i = ptid; i < w.natom; i += NPT) {
-      if (box_d2(S.p_bb, w.atom_xyz[3 * i], w.atom_xyz[3 * i + 1], w.atom_xyz[3 * i + 2]) <= 1.0001e-10) {
-        int k = atomicAdd(&S.p_int[1], 1);
-        if (k < 16) s_nuc_tmp[k] = i;
-      }
-    }
-    named_bar_sync(2, NPT);
-    const int nnuc = S.p_int[1];
-
-    for (int sub = 0; sub < nsub_a * nsub_b * nsub_c; sub++) {
-      const int ta0 = sa0 + (sub % nsub_a) * g.ta, tb0 = sb0 + ((sub / nsub_a) % nsub_b) * g.tb;
-      const int tc0 = sc0 + (sub / (nsub_a * nsub_b)) * g.tc;
-      if (ta0 >= na || tb0 >= nb || tc0 >= g.c1) continue;
-      const int tslot = tcount % C::TSLOTS;
-      tcount++;
-      double *tp = S.s_pt + tslot * 4 * P;
-      // ---- points of the sub-tile -> tile-info slot (safe: consumers are at most NS sub-tiles behind) --------------
-      {
-        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-        if (ptid < P) {
-          int a = ta0 + ptid % g.ta, b = tb0 + (ptid / g.ta) % g.tb, c = tc0 + ptid / (g.ta * g.tb);
-          bool valid = a < na && b < nb && c < g.c1;
-          double x[3] = {0, 0, 0}, wc[3], wcr[3] = {0, 0, 0};
-          if (valid) {
-            grid_point(g, a, b, c, x);
-            grd_wrap(p.xf, x, g.periodic, wc, wcr);
-#pragma unroll
-            for (int d = 0; d < 3; d++) { lo[d] = wcr[d]; hi[d] = wcr[d]; }
-          }
-          tp[ptid] = wcr[0]; tp[P + ptid] = wcr[1]; tp[2 * P + ptid] = wcr[2];
-          tp[3 * P + ptid] = valid ? 1.0 : 0.0;
-        }
-        if (ptid == 0) {
-          WsTileInfo &ti = S.tinfo[tslot];
-          ti.a0 = ta0; ti.b0 = tb0; ti.c0 = tc0; ti.nnuc = nnuc;
-          for (int k = 0; k < 16 && k < nnuc; k++) ti.nuc[k] = s_nuc_tmp[k];
-        }
-        ws_prod_bbox<C>(lo, hi, S, S.p_bb + 6, ptid);
-      }
-      // ---- S2: refine against the sub-tile box, expand to (primitive, shell) pairs (ordered) ------------------------
-      int kact = 0;
-      for (int base = 0; base < ns; base += NPT) {
-        int j = base + ptid, cnt = 0, pb = 0, s = 0;
-        if (j < ns) {
-          s = sh_list[j];
-          double4 xa = w.shell_xa[s];
-          if (box_d2(S.p_bb + 6, xa.x, xa.y, xa.z) <= w.shell_cut[s].y * (1.0 + 1e-12)) {
-            pb = w.shell_pbeg[s];
-            cnt = w.shell_pbeg[s + 1] - pb;
-          }
-        }
-        int incl = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          int v = __shfl_up_sync(~0u, incl, o);
-          if (lane >= o) incl += v;
-        }
-        if (lane == 31) S.p_cnt[warp] = incl;
-        named_bar_sync(2, NPT);
-        int off = kact, tot = 0;
-#pragma unroll
-        for (int i = 0; i < NPW; i++) {
-          if (i < warp) off += S.p_cnt[i];
-          tot += S.p_cnt[i];
-        }
-        off += incl - cnt;
-        if (cnt > 0) {
-          const double4 xa = w.shell_xa[s];
-          const double2 cut = w.shell_cut[s];
-          for (int i = 0; i < cnt; i++) {
-            pr_list[off + i] = make_int2(pb + i, s);
-            const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[pb + i];
-            const long long bits = (long long)s | ((long long)l.x << 32) | ((long long)l.y << 40) | ((long long)l.z << 48);
-            double4 *r = reinterpret_cast<double4 *>(rec + (size_t)(off + i) * 8);
-            r[0] = xa;
-            r[1] = make_double4(cut.x, cut.y, __longlong_as_double(bits), 0.0);
-          }
-        }
-        kact += tot;
-        named_bar_sync(2, NPT);
-      }
-      __threadfence_block();
-      named_bar_sync(2, NPT);   // pr_list (global scratch) visible to every producer thread
-      const int nch = (kact + KC - 1) / KC;
-      const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
-      const bool pvalid = tp[3 * P + pt] != 0.0;
-
-      if (kact == 0) {   // nothing active: a data-less stage tells the consumers to emit zeros (+ EDF) for this tile
-        const int stg = acquire();
-        if (ptid == 0) {
-          mbar_expect_tx(&S.full[stg], 0u);   // warp 0's second arrival (the one that carries the TMA byte count)
-          WsStageHdr &h = S.hdr[stg];
-          h.flags = 1 | 2 | 4 | 8; h.blk = 0; h.tslot = tslot;
-        }
-        publish(stg);
-        continue;
-      }
-      auto load_rec = [&](int cc) -> double2 {
-        return reinterpret_cast<const double2 *>(rec + (size_t)(cc * KC + grp * 4) * 8)[pt];
-      };
-      double2 rec_next = make_double2(0.0, 0.0);
-      double *agbase = p.acache + ((size_t)blockIdx.x * 2 + (tcount & 1)) * (size_t)p.acache_chunks * C::A_STAGE;
-      int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + (tcount & 1)) * (size_t)p.acache_chunks * 8;
-      for (int blk = 0; blk < p.nblk; blk++) {
-        if (blk == 1) {   // bulk stores of the chi tiles complete, k-quad masks visible -> safe to read them back
-          if (ptid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-          __threadfence();
-          named_bar_sync(2, NPT);
-        }
-        if (blk == 0 || nch > p.acache_chunks) rec_next = load_rec(blk == 0 ? 0 : p.acache_chunks);
-        for (int c = 0; c < nch; c++) {
-          const int stg = acquire();
-          const bool cached = c < p.acache_chunks;           // this chunk's chi tile lives in the L2 cache
-          const bool compute = blk == 0 || !cached;
-          const bool save = blk == 0 && cached && p.nblk > 1;
-          // B rows: one bulk TMA copy per active primitive of the chunk (warp 0: lane = row); A tile from the cache
-          const int nrow = min(KC, kact - c * KC);
-          if (warp == 0) {
-            if (lane == 0)
-              mbar_expect_tx(&S.full[stg], (uint32_t)(nrow * NB * sizeof(double)) +
-                                               (compute ? 0u : (uint32_t)(C::A_STAGE * sizeof(double))));
-            __syncwarp();
-            if (lane < nrow) {
-              const int prim = pr_list[c * KC + lane].x;
-              tma_bulk_g2s(S.Bs + stg * C::B_STAGE + lane * SB, w.cmoT + (size_t)prim * w.ldc + (size_t)blk * NB,
-                           (uint32_t)(NB * sizeof(double)), &S.full[stg]);
-            }
-            if (!compute) {
-              if (lane == 0)
-                tma_bulk_g2s(S.As + stg * C::A_STAGE, agbase + (size_t)c * C::A_STAGE,
-                             (uint32_t)(C::A_STAGE * sizeof(double)), &S.full[stg]);
-              if (lane < C::NKQ) S.hdr[stg].nzmask[lane] = nzbase[c * 8 + lane];
-            }
-            if (lane == 0) {
-              WsStageHdr &h = S.hdr[stg];
-              h.flags = (c == 0 ? 1 : 0) | (c == nch - 1 ? 2 : 0) | ((c == nch - 1 && blk == p.nblk - 1) ? 4 : 0);
-              h.blk = blk; h.tslot = tslot;
-            }
-          }
-          if (compute) {
-            // A tile: this 16-lane group evaluates the 4 primitives of k-quad `grp` at its 16 points.  The quad's four
-            // records (256 contiguous bytes) were loaded one chunk ahead, 16 bytes per lane, and are passed round
-            // with shuffles: no dependent global load sits between acquiring the stage and the arithmetic.
-            const double2 mine = rec_next;
-            if (c + 1 < nch) rec_next = load_rec(c + 1);
-            const size_t aoffq = (size_t)(grp * ND) * P * 4 + pt * 4;
-            double *Aq = S.As + stg * C::A_STAGE + aoffq;
-            unsigned nzbits = 0;
-            int prev_sh = -1;
-            double dx = 0, dy = 0, dz = 0, ex = 0, al = 0;
-            bool pass = false;
-            const int sbase = lane & 16;
-#pragma unroll
-            for (int k4 = 0; k4 < 4; k4++) {
-              const int gk = c * KC + grp * 4 + k4;
-              const double rx = __shfl_sync(~0u, mine.x, sbase + k4 * 4), ry = __shfl_sync(~0u, mine.y, sbase + k4 * 4);
-              const double rz = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 1), ra = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 1);
-              const double rc = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 2), rc2 = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 2);
-              const long long bits = __double_as_longlong(__shfl_sync(~0u, mine.x, sbase + k4 * 4 + 3));
-              double chi[ND];
-#pragma unroll
-              for (int d = 0; d < ND; d++) chi[d] = 0.0;
-              if (gk < kact && pvalid) {
-                const int sh = (int)(bits & 0xffffffffll);
-                if (sh != prev_sh) {   // new shell: distance screen (:2747) and exponential (:2749) shared by its primitives
-                  prev_sh = sh;
-                  dx = px - rx; dy = py - ry; dz = pz - rz;
-                  al = ra;
-                  const double d2 = dx * dx + dy * dy + dz * dz;
-                  pass = within_cut(dx, dy, dz, d2, rc, rc2);
-                  ex = pass ? exp(-al * d2) : 0.0;
-                }
-                if (pass) {
-                  prim_chi<ND>(dx, dy, dz, (int)((bits >> 32) & 0xff), (int)((bits >> 40) & 0xff), (int)((bits >> 48) & 0xff),
-                               al, ex, chi);
-                  nzbits |= 1u;
-                }
-              }
-              const int sw = k4 ^ ((pt >> 2) & 3);
-#pragma unroll
-              for (int d = 0; d < ND; d++) Aq[d * P * 4 + sw] = chi[d];
-            }
-            // k-quad mask: bit wm set if any of the 8 points of row group wm has an unmasked primitive in this quad
-            const unsigned bal = __ballot_sync(~0u, nzbits != 0);
-            const unsigned half = (bal >> (lane & 16)) & 0xffffu;
-            if (pt == 0) {
-              const int m = ((half & 0xffu) ? 1 : 0) | ((half & 0xff00u) ? 2 : 0);
-              S.hdr[stg].nzmask[grp] = m;
-              if (save) nzbase[c * 8 + grp] = m;
-            }
-            if (save) {
-              // copy the finished tile to the L2 cache with one bulk TMA store (shared -> global)
-              fence_proxy_async();
-              named_bar_sync(2, NPT);
-              if (ptid == 0) {
-                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous store has read its stage
-                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(agbase + (size_t)c * C::A_STAGE),
-                             "r"(smem_u32(S.As + stg * C::A_STAGE)), "r"((uint32_t)(C::A_STAGE * sizeof(double)))
-                             : "memory");
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-              }
-            }
-          }
-          publish(stg);
-        }
-      }
-    }
-  }
-  // exit stage
-  {
-    const int stg = acquire();
-    if (ptid == 0) {
-      mbar_expect_tx(&S.full[stg], 0u);
-      S.hdr[stg].flags = 16; S.hdr[stg].blk = 0; S.hdr[stg].tslot = 0;
-    }
-    publish(stg);
-  }
-}
 // ---------------------------------------------------------------------------------------------------------------
-// Split producer (config "WG").  ncu on the version above: the consumers still waited ~17 % of the time on the
-// stages whose chi tile had to be computed (MO block 0), while the producer warps idled ~60 % of the time during the
-// cached blocks.  Here the two jobs are decoupled:
+// Split producer.  An earlier version let all four producer warps compute the chi tile of MO block 0 straight into
+// the stage and reload it from the L2 cache for blocks 1..6: ncu showed the consumers waiting ~17 % of the time on
+// the computed stages while the producers idled ~60 % of the time during the cached blocks (74 % of the DMMA peak).
+// Decoupling the two jobs took the same slab to 84 %:
 //   * GENERATOR warps (3, named barrier 2 with 96 threads) run one sub-tile AHEAD: claim super-tiles, screen shells,
 //     evaluate chi for every active primitive of the sub-tile and write the tiles (in the shared-memory layout of an
 //     A stage) straight to the per-CTA L2 cache buffer `tcount & 1`;
@@ -667,10 +372,11 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
           const int nrow = min(KC, td.kact - c * KC);
           const int prim = lane < nrow ? pr_list[c * KC + lane].x : 0;         // loads issued before the wait
           const int nz = lane < C::NKQ ? nzbase[c * 8 + lane] : 0;
+          const unsigned m0 = __ballot_sync(~0u, (nz & 1) != 0), m1 = __ballot_sync(~0u, (nz & 2) != 0);
           const int stg = acquire();
-          if (lane < C::NKQ) S.hdr[stg].nzmask[lane] = nz;
           if (lane == 0) {
             WsStageHdr &h = S.hdr[stg];
+            h.kqmask[0] = (int)m0; h.kqmask[1] = (int)m1;
             h.flags = (c == 0 ? 1 : 0) | (c == td.nch - 1 ? 2 : 0) | ((c == td.nch - 1 && blk == p.nblk - 1) ? 4 : 0);
             h.blk = blk; h.tslot = td.tslot;
           }
@@ -707,44 +413,68 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Consumer side: 256 threads, named barrier 1
+// Consumer side: 256 threads, named barrier 1.  Warps 0..3 (warp columns 0,1) own 4 fragments each and run with 232
+// registers, warps 4..7 (warp columns 2,3) own 3 fragments and run with 184: every SM sub-partition carries 4 + 3 = 7
+// of the 14 fragments of an MO block.
 // ---------------------------------------------------------------------------------------------------------------
-// MMAs of one stage for a consumer warp that owns NF fragments (8-column groups) of the MO block.
+// MMAs of one stage.  kqm: bit kq set if k-quad kq has an unmasked (point, primitive) pair in this warp's 8 points.
+// Operands of the next k-quad / derivative row are fetched from shared memory while the current DMMAs issue, so the
+// tensor pipe does not drain between k-quads (the first version reloaded everything at the top of each k-quad and
+// spilled accumulators: ~8 % of the in-loop time was both warps of a sub-partition waiting on operands).
 template <class C, int NF>
-__device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][C::NI][2], const double *Ast, const double *Bst,
-                                             const int *nzmask, int wm) {
+__device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const double *Ast, const double *Bst, unsigned kqm) {
   constexpr int ND = C::ND, P = C::P, SB = C::SB;
-#pragma unroll 1
-  for (int kq = 0; kq < C::NKQ; kq++) {
-    if (!((nzmask[kq] >> wm) & 1)) continue;             // all 8 points x 4 primitives masked (warp-uniform)
-    double b[NF];
+  if (kqm == 0) return;                                  // all 8 points x 32 primitives masked (warp-uniform)
+  int kq = __ffs(kqm) - 1;
+  kqm &= kqm - 1;
+  double b[NF];
 #pragma unroll
-    for (int ni = 0; ni < NF; ni++) b[ni] = Bst[kq * 4 * SB + ni * 8];
+  for (int ni = 0; ni < NF; ni++) b[ni] = Bst[kq * 4 * SB + ni * 8];
+  const double *Ak = Ast + (size_t)kq * ND * P * 4;
+  double a = Ak[0];
+  bool more;
+#pragma unroll 1
+  do {
+    more = kqm != 0;
+    const int kqn = more ? __ffs(kqm) - 1 : kq;
+    kqm &= kqm - 1;
+    double bn[NF];
+#pragma unroll
+    for (int ni = 0; ni < NF; ni++) bn[ni] = Bst[kqn * 4 * SB + ni * 8];
+    const double *An = Ast + (size_t)kqn * ND * P * 4;
 #pragma unroll
     for (int d = 0; d < ND; d++) {
-      const double a = Ast[(size_t)(kq * ND + d) * P * 4];
+      const double an = (d + 1 < ND) ? Ak[(d + 1) * P * 4] : An[0];
 #pragma unroll
       for (int ni = 0; ni < NF; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
+      a = an;
     }
-  }
+#pragma unroll
+    for (int ni = 0; ni < NF; ni++) b[ni] = bn[ni];
+    Ak = An;
+    kq = kqn;
+  } while (more);
 }
 
-template <class C>
+template <class C, int NF>
 __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) {
-  constexpr int ND = C::ND, P = C::P, NS = C::NS, NB = C::NB, SB = C::SB, NI = C::NI, NCT = C::NCT, NKQ = C::NKQ;
+  constexpr int ND = C::ND, P = C::P, NS = C::NS, NB = C::NB, SB = C::SB, NCT = C::NCT;
   const int lane = ctid & 31, cw = ctid >> 5;
   const int wm = cw & 1, wn = cw >> 1;                 // row group (8 points) and warp column (0..3)
-  const int nfw = wn < 2 ? 4 : 3;                      // fragments of this warp: 4,4,3,3 -> 7 per SM sub-partition
-  const int f0 = wn < 2 ? wn * 4 : 8 + (wn - 2) * 3;
+  const int f0 = wn < 2 ? wn * 4 : 8 + (wn - 2) * 3;   // first fragment of this warp: 4,4,3,3 fragments
   const int row = lane >> 2;
   const int aoff = row * 4 + ((lane & 3) ^ (((wm * 8 + row) >> 2) & 3));
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
-  double acc[ND][NI][2];
+  double acc[ND][NF][2];
+  double q[ND];                                         // this thread's share of the quadratic forms of the sub-tile
 #pragma unroll
-  for (int d = 0; d < ND; d++)
+  for (int d = 0; d < ND; d++) {
+    q[d] = 0.0;
 #pragma unroll
-    for (int ni = 0; ni < NI; ni++) acc[d][ni][0] = acc[d][ni][1] = 0.0;
+    for (int ni = 0; ni < NF; ni++) acc[d][ni][0] = acc[d][ni][1] = 0.0;
+  }
+  unsigned tpar = 0;                                    // sub-tile parity: s_part is double-buffered
 
   for (unsigned it = 0;; it++) {
     const int stg = it % NS;
@@ -755,24 +485,21 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     if (!(flags & 8)) {
       const double *Ast = S.As + stg * C::A_STAGE + (size_t)wm * 32 + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
-      // warp-uniform choice of the fragment count: a predicated-off DMMA still occupies the tensor pipe
-      if (nfw == 4) ws_mma_stage<C, 4>(acc, Ast, Bst, h.nzmask, wm);
-      else ws_mma_stage<C, 3>(acc, Ast, Bst, h.nzmask, wm);
+      ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&S.empty[stg]);           // stage (and its header) no longer needed by this warp
     if (!(flags & 2)) continue;
 
-    // ---- end of an MO block: occupation-weighted quadratic forms of this thread's MOs (:2091-2147) ---------------
+    // ---- end of an MO block: occupation-weighted quadratic forms of this thread's MOs (:2091-2147).  No barrier:
+    // the partial sums stay in registers until the end of the sub-tile, so the warps drift apart and one warp's
+    // epilogue overlaps the other warps' MMAs. ------------------------------------------------------------------------
     if (!(flags & 8)) {
-      double q[ND];
 #pragma unroll
-      for (int d = 0; d < ND; d++) q[d] = 0.0;
-#pragma unroll
-      for (int ni = 0; ni < NI; ni++)
+      for (int ni = 0; ni < NF; ni++)
 #pragma unroll
         for (int j = 0; j < 2; j++) {
-          const double oc = (ni < 3 || nfw == 4) ? w.occ[blk * NB + (f0 + ni) * 8 + 2 * (lane & 3) + j] : 0.0;
+          const double oc = w.occ[blk * NB + (f0 + ni) * 8 + 2 * (lane & 3) + j];
           const double v0 = acc[0][ni][j];
           q[0] += oc * v0 * v0;
           if (ND > 1) {
@@ -792,41 +519,40 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
           }
         }
 #pragma unroll
-      for (int d = 0; d < ND; d++) {
-        q[d] += __shfl_xor_sync(~0u, q[d], 1);
-        q[d] += __shfl_xor_sync(~0u, q[d], 2);
-      }
-      if ((lane & 3) == 0) {
-#pragma unroll
-        for (int d = 0; d < ND; d++) S.s_part[(((blk & 1) * 4 + wn) * P + wm * 8 + row) * ND + d] = q[d];
-      }
-#pragma unroll
       for (int d = 0; d < ND; d++)
 #pragma unroll
-        for (int ni = 0; ni < NI; ni++) acc[d][ni][0] = acc[d][ni][1] = 0.0;
-    }
-    named_bar_sync(1, NCT);
-    if (!(flags & 8) && ctid < P * ND) {                 // fixed-order fold of the four warp columns
-      double sum = S.s_tot[ctid];
-#pragma unroll
-      for (int v = 0; v < 4; v++) sum += S.s_part[((blk & 1) * 4 + v) * P * ND + ctid];
-      S.s_tot[ctid] = sum;
+        for (int ni = 0; ni < NF; ni++) acc[d][ni][0] = acc[d][ni][1] = 0.0;
     }
     if (!(flags & 4)) continue;
 
-    // ---- end of the sub-tile: EDF core, nucleus test, derived quantities, stores ---------------------------------
+    // ---- end of the sub-tile: fold the partial sums (fixed order: lanes, then warp columns), EDF core, nucleus test,
+    // derived quantities, stores ------------------------------------------------------------------------------------------
+    double *part = S.s_part + tpar * 4 * P * ND;         // [4 warp columns][P][ND]
+    double *other = S.s_part + (tpar ^ 1u) * 4 * P * ND; // free until the next sub-tile ends (EDF scratch)
+    tpar ^= 1u;
+#pragma unroll
+    for (int d = 0; d < ND; d++) {
+      q[d] += __shfl_xor_sync(~0u, q[d], 1);
+      q[d] += __shfl_xor_sync(~0u, q[d], 2);
+    }
+    if ((lane & 3) == 0) {
+#pragma unroll
+      for (int d = 0; d < ND; d++) part[(wn * P + wm * 8 + row) * ND + d] = q[d];
+    }
+#pragma unroll
+    for (int d = 0; d < ND; d++) q[d] = 0.0;
     named_bar_sync(1, NCT);
     const double *tp = S.s_pt + tslot * 4 * P;
     const WsTileInfo &ti = S.tinfo[tslot];
-    if (w.nedf > 0) {
-      const int pt = ctid & 15, slot = ctid >> 4;        // 8 slots (threads 0..127) through the free s_part area
-      if (ctid < 128) {
+    if (w.nedf > 0) {                                    // core densities of ECP wavefunctions (calculate_edf, :2783)
+      const int pt = ctid & 15, slot = ctid >> 4;        // 4 slots (threads 0..63)
+      if (ctid < 64) {
         double e[ND];
 #pragma unroll
         for (int d = 0; d < ND; d++) e[d] = 0.0;
         if (tp[3 * P + pt] != 0.0) {
           const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
-          for (int i = slot; i < w.nedf; i += 8) {
+          for (int i = slot; i < w.nedf; i += 4) {
             const double4 xa = w.edf_xa[i];
             const double4 cc = w.edf_cc[i];
             const double dx = px - xa.x, dy = py - xa.y, dz = pz - xa.z;
@@ -840,19 +566,24 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
           }
         }
 #pragma unroll
-        for (int d = 0; d < ND; d++) S.s_part[(slot * P + pt) * ND + d] = e[d];
-      }
-      named_bar_sync(1, NCT);
-      if (ctid < P * ND) {
-        double sum = S.s_tot[ctid];
-        for (int v = 0; v < 8; v++) sum += S.s_part[v * P * ND + ctid];
-        S.s_tot[ctid] = sum;
+        for (int d = 0; d < ND; d++) other[(slot * P + pt) * ND + d] = e[d];
       }
       named_bar_sync(1, NCT);
     }
     if (ctid < P) {
-      double *t = S.s_tot + ctid * ND;
       if (tp[3 * P + ctid] != 0.0) {
+        double t[ND];
+#pragma unroll
+        for (int d = 0; d < ND; d++) {
+          double sum = 0.0;
+#pragma unroll
+          for (int v = 0; v < 4; v++) sum += part[(v * P + ctid) * ND + d];
+          if (w.nedf > 0) {
+#pragma unroll
+            for (int v = 0; v < 4; v++) sum += other[(v * P + ctid) * ND + d];
+          }
+          t[d] = sum;
+        }
         const int a = ti.a0 + ctid % g.ta, b = ti.b0 + (ctid / g.ta) % g.tb, c = ti.c0 + ctid / (g.ta * g.tb);
         double f = t[0], gx = 0, gy = 0, gz = 0, hs[6] = {0, 0, 0, 0, 0, 0};
         if (ND > 1) { gx = t[ND > 1 ? 1 : 0]; gy = t[ND > 1 ? 2 : 0]; gz = t[ND > 1 ? 3 : 0]; }
@@ -876,53 +607,51 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
         }
         emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs, isnuc, p.nci_const);
       }
-#pragma unroll
-      for (int d = 0; d < ND; d++) t[d] = 0.0;           // ready for the next sub-tile
     }
+    if (w.nedf > 0) named_bar_sync(1, NCT);              // EDF scratch (the other s_part buffer) free again
   }
 }
 
-template <class C, bool SPLIT>
+template <class C>
 __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant__ WfnParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t s_full[C::NS], s_empty[C::NS];
+  __shared__ __align__(8) uint64_t s_full[C::NS], s_empty[C::NS], s_ready[2], s_freeb[2];
   __shared__ WsStageHdr s_hdr[C::NS];
   __shared__ WsTileInfo s_tinfo[C::TSLOTS];
+  __shared__ WsTileDesc s_tdesc[2];
   __shared__ double s_pred[C::NPW * 6], s_pbb[12];
   __shared__ int s_pcnt[C::NPW], s_pint[4];
-  __shared__ __align__(8) uint64_t s_ready[2], s_freeb[2];
-  __shared__ WsTileDesc s_tdesc[2];
   WsShared<C> S;
   S.As = reinterpret_cast<double *>(smem_raw);
   S.Bs = S.As + C::NS * C::A_STAGE;
   S.s_part = S.Bs + C::NS * C::B_STAGE;
-  S.s_tot = S.s_part + C::NPART;
-  S.s_pt = S.s_tot + C::P * C::ND;
+  S.s_pt = S.s_part + C::NPART;
   S.full = s_full; S.empty = s_empty; S.hdr = s_hdr; S.tinfo = s_tinfo;
   S.p_red = s_pred; S.p_bb = s_pbb; S.p_cnt = s_pcnt; S.p_int = s_pint;
   S.ready = s_ready; S.freeb = s_freeb; S.tdesc = s_tdesc;
   const int tid = threadIdx.x;
   if (tid == 0) {
     for (int s = 0; s < C::NS; s++) {
-      // unsplit: one arrival per producer warp + the expect_tx arrival of warp 0; split: the streamer's expect_tx
-      mbar_init(&s_full[s], SPLIT ? 1 : C::NPW + 1);
+      mbar_init(&s_full[s], 1);            // the streamer's arrive.expect_tx (+ the TMA byte count)
       mbar_init(&s_empty[s], C::NCW);      // one arrival per consumer warp
     }
     for (int b = 0; b < 2; b++) { mbar_init(&s_ready[b], 1); mbar_init(&s_freeb[b], 1); }
     fence_mbar_init();
   }
   for (int i = tid; i < C::NS * C::B_STAGE; i += C::NT) S.Bs[i] = 0.0;   // stale rows stay finite (they meet chi = 0)
-  for (int i = tid; i < C::P * C::ND; i += C::NT) S.s_tot[i] = 0.0;
   fence_proxy_async();
   __syncthreads();
+  // setmaxnreg works per warpgroup (4 warps): 128 x (232 + 184 + 88) = 64512 registers = 384 x 168, the launch figure
   if (tid >= C::NCT) {
     reg_dec<C::REG_PROD>();
-    if (!SPLIT) ws_producer<C>(p, S, tid - C::NCT);
-    else if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
+    if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
     else ws_generator<C>(p, S, tid - C::NCT - 32);
+  } else if (tid < 128) {
+    reg_inc<C::REG_CONS4>();
+    ws_consumer<C, 4>(p, S, tid);
   } else {
-    reg_inc<C::REG_CONS>();
-    ws_consumer<C>(p, S, tid);
+    reg_inc<C::REG_CONS3>();
+    ws_consumer<C, 3>(p, S, tid);
   }
 }
 #endif
