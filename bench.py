@@ -265,8 +265,13 @@ def run_ours(a):
                            "l2": "256 MiB flush write between steps; outputs 5.1 GB/step >> 126 MB L2",
                            "kernel": cfg},
                 "roofline": {"bound": "tensor", "achieved": ach, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
-                             "frac": ach / FP64_PEAK_TFLOPS, "traffic": None,
-                             "kernel": f"wfn_grid_kernel cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, P={cfg['points_per_tile']}, NB={cfg['mo_block']})", "kernel_ms": kms,
+                             "frac": ach / FP64_PEAK_TFLOPS,
+                             # dram__bytes_read.sum + dram__bytes_write.sum of one whole-grid launch on one GPU (ncu,
+                             # profiles/r1_ncu_dram_wfn_ws_kernel_400.txt): chi-tile cache spills, not algorithmic bytes
+                             "traffic": 1.026e13 if (a.n == 400 and world == 1 and cfg["cfg"] == 6) else None,
+                             "traffic_unit": "bytes/launch",
+                             "kernel": f"{'wfn_ws_kernel' if cfg['cfg'] == 6 else 'wfn_grid_kernel'} cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, "
+                                       f"P={cfg['points_per_tile']}, NB={cfg['mo_block']})", "kernel_ms": kms,
                              "algorithmic_flops_per_launch": flops, "mean_n_act": nact / max(mypts, 1),
                              "peak_source": "measured FP64 mma.sync (DMMA) peak, profiles/r1_fp64_peak_microbench.log; "
                                             "MEASURED_PEAKS.json holds no FP64 figure"},

@@ -368,7 +368,10 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
       it++;
     } else {
       for (int blk = 0; blk < p.nblk; blk++) {
-        for (int c = 0; c < td.nch; c++) {
+        for (int cc = 0; cc < td.nch; cc++) {
+          // odd MO blocks walk the chunks backwards: the chi tiles of a sub-tile (~0.65 MB per CTA, x 148 CTAs x 2
+          // buffers) exceed the L2, and a cyclic re-read would miss every time; the zigzag re-uses the most recent ones
+          const int c = (blk & 1) ? td.nch - 1 - cc : cc;
           const int nrow = min(KC, td.kact - c * KC);
           const int prim = lane < nrow ? pr_list[c * KC + lane].x : 0;         // loads issued before the wait
           const int nz = lane < C::NKQ ? nzbase[c * 8 + lane] : 0;
@@ -377,7 +380,7 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
           if (lane == 0) {
             WsStageHdr &h = S.hdr[stg];
             h.kqmask[0] = (int)m0; h.kqmask[1] = (int)m1;
-            h.flags = (c == 0 ? 1 : 0) | (c == td.nch - 1 ? 2 : 0) | ((c == td.nch - 1 && blk == p.nblk - 1) ? 4 : 0);
+            h.flags = (cc == 0 ? 1 : 0) | (cc == td.nch - 1 ? 2 : 0) | ((cc == td.nch - 1 && blk == p.nblk - 1) ? 4 : 0);
             h.blk = blk; h.tslot = td.tslot;
           }
           __syncwarp();
