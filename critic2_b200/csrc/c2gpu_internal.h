@@ -26,10 +26,10 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
 cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &xf, unsigned long long *count,
                              cudaStream_t st);
 cudaError_t promol_launch(int nd, const PromolParams &p, int grid, cudaStream_t st);
-cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, double rhocut,
+cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, int nfrag,
+                               const double *rhofrag, double rhoparam, double rhoparam2, double rhocut,
                                double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
-                               double *raw_sums /*host[3]*/, long *ndat /*host*/, double *dat_dev, long maxdat,
-                               cudaStream_t st);
+                               double *raw_sums, long *ndat, double *dat_dev, long maxdat, cudaStream_t st);
 
 extern long g_launches;       // kernels launched by the library
 

@@ -26,6 +26,9 @@ struct CutArgs {
   const double *rhoat;
   double rhocut100, dimcut, rhoplot100, sr0, sr1, rho_void;
   int onlyneg;
+  int nfrag;                 // fragments (:579-582): rhofrag is [nfrag][npts]
+  const double *rhofrag;
+  double rhoparam, rhoparam2;
 };
 
 __device__ __forceinline__ void cut_point(const CutArgs &a, long i, bool &isdat, bool &mask, double &q, double &qp,
@@ -34,10 +37,16 @@ __device__ __forceinline__ void cut_point(const CutArgs &a, long i, bool &isdat,
   cg = a.cgrad[i];
   bool inter = true;
   q = 0.0; qp = 0.0; v = 0.0;
-  if (a.rho_void > 0.0) {                                            // :573-582
+  if (a.nfrag > 0) {                                                 // :579-582
+    double s = 0.0;
+    for (int f = 0; f < a.nfrag; f++) s += a.rhofrag[(size_t)f * a.npts + i];
+    inter = s >= a.rhoparam2 * a.rhoat[i];
+    for (int f = 0; f < a.nfrag; f++) inter = inter && (a.rhofrag[(size_t)f * a.npts + i] <= s * a.rhoparam);
+  }
+  if (a.rho_void > 0.0) {                                            // :583-590
     double ra = a.rhoat[i];
-    inter = ra < a.rho_void;
-    if (inter) { q = fabs(cr) / 100.0; qp = ra; v = 1.0; }
+    inter = inter && ra < a.rho_void;
+    if (ra < a.rho_void) { q = fabs(cr) / 100.0; qp = ra; v = 1.0; }
   }
   isdat = fabs(cr) < a.rhocut100 && cg < a.dimcut && inter;          // :593
   mask = fabs(cr) > a.rhoplot100 || !inter;                          // :596
@@ -138,22 +147,25 @@ __global__ void __launch_bounds__(CUT_NT) cut_emit_kernel(CutArgs a, const unsig
   }
 }
 
-cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, double rhocut,
+cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, int nfrag,
+                               const double *rhofrag, double rhoparam, double rhoparam2, double rhocut,
                                double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
                                double *raw_sums, long *ndat, double *dat_dev, long maxdat, cudaStream_t st) {
   raw_sums[0] = raw_sums[1] = raw_sums[2] = 0.0;
   *ndat = 0;
   if (npts <= 0) return cudaSuccess;
-  CutArgs a{npts, crho, cgrad, rhoat, rhocut * 100.0, dimcut, rhoplot * 100.0, sr0 * 100.0, sr1 * 100.0, rho_void, onlyneg};
+  CutArgs a{npts, crho, cgrad, rhoat, rhocut * 100.0, dimcut, rhoplot * 100.0, sr0 * 100.0, sr1 * 100.0, rho_void, onlyneg,
+            nfrag, rhofrag, rhoparam, rhoparam2};
   int nblk = (int)((npts + CUT_BLK - 1) / CUT_BLK);
-  unsigned *bcount = nullptr;
-  unsigned long long *boff = nullptr;
-  double *bsum = nullptr, *out = nullptr;
+  // one scratch allocation: out[4] | bsum[3*nblk] | boff[nblk] (64-bit) | bcount[nblk]
+  unsigned char *scr = nullptr;
+  const size_t o_bsum = 4 * sizeof(double), o_boff = o_bsum + sizeof(double) * 3 * (size_t)nblk;
+  const size_t o_bcount = o_boff + sizeof(unsigned long long) * (size_t)nblk;
   cudaError_t e;
-  if ((e = cudaMalloc(&bcount, sizeof(unsigned) * nblk)) != cudaSuccess) return e;
-  if ((e = cudaMalloc(&boff, sizeof(unsigned long long) * nblk)) != cudaSuccess) return e;
-  if ((e = cudaMalloc(&bsum, sizeof(double) * 3 * nblk)) != cudaSuccess) return e;
-  if ((e = cudaMalloc(&out, sizeof(double) * 4)) != cudaSuccess) return e;
+  if ((e = cudaMalloc(&scr, o_bcount + sizeof(unsigned) * (size_t)nblk)) != cudaSuccess) return e;
+  double *out = reinterpret_cast<double *>(scr), *bsum = reinterpret_cast<double *>(scr + o_bsum);
+  unsigned long long *boff = reinterpret_cast<unsigned long long *>(scr + o_boff);
+  unsigned *bcount = reinterpret_cast<unsigned *>(scr + o_bcount);
   cut_count_kernel<<<nblk, CUT_NT, 0, st>>>(a, bcount, bsum);
   cut_scan_kernel<<<1, 1024, 0, st>>>(nblk, bcount, boff, bsum, out);
   cut_emit_kernel<<<nblk, CUT_NT, 0, st>>>(a, boff, dat_dev, maxdat);
@@ -161,7 +173,7 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
   double h[4];
   e = cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(bcount); cudaFree(boff); cudaFree(bsum); cudaFree(out);
+  cudaFree(scr);
   if (e != cudaSuccess) return e;
   *ndat = (long)h[0];
   raw_sums[0] = h[1]; raw_sums[1] = h[2]; raw_sums[2] = h[3];

@@ -59,15 +59,25 @@ class NciOptions:
     onlyneg: bool = False
     rho_void: float = -1.0
     xinc: float = 0.1
+    rhoparam: float = 0.95        # fragments: :120-121, used by the `inter` test :579-582
+    rhoparam2: float = 0.75
 
     @staticmethod
     def promolecular():
         return NciOptions(rhocut=0.2, dimcut=1.0, rhoplot=0.12, dimplot=0.3, isden=False)
 
 
-def nci_grid(st: Structure, nstep=None, xinc: float = 0.1, rthres: float | None = None):
-    """NCIPLOT box and step (no fragments): nci@proc.f90:122-134, 350-410.  Returns (x0, xmat, nstep)."""
-    if st.ismolecule:
+def nci_grid(st: Structure, nstep=None, xinc: float = 0.1, rthres: float | None = None, frag_xyz=None):
+    """NCIPLOT box and step: nci@proc.f90:122-134, 350-410.  Returns (x0, xmat, nstep).
+    frag_xyz: list of (nat,3) Cartesian fragment coordinates -> the box is the fragments' bounding box (findlimits = 1,
+    :350-364, non-periodic) and rthres defaults to 2 bohr (:159, ithres = 1 :321)."""
+    if frag_xyz is not None:
+        allr = np.concatenate([np.asarray(r, float).reshape(-1, 3) for r in frag_xyz])
+        x0, x1 = allr.min(0), allr.max(0)
+        periodic = False
+        if rthres is None:
+            rthres = 2.0
+    elif st.ismolecule:
         x0 = st.m_x2c @ st.molborder
         x1 = st.m_x2c @ (1.0 - st.molborder)
         periodic = False
@@ -106,16 +116,23 @@ def nci_grid(st: Structure, nstep=None, xinc: float = 0.1, rthres: float | None 
 
 
 def nciplot(field: "gpu._Field", st: Structure, nstep=None, opts: NciOptions | None = None,
-            promol: "gpu._Field | None" = None, rthres: float | None = None):
-    """NCIPLOT evaluation + cutoff pass.  Returns dict(crho, cgrad, rhoat, sums, dat, ndat, grid)."""
+            promol: "gpu._Field | None" = None, rthres: float | None = None, fragments=None, frag_xyz=None):
+    """NCIPLOT evaluation + cutoff pass.  Returns dict(crho, cgrad, rhoat, rhofrag, sums, dat, ndat, grid).
+    fragments: list of gpu.FragmentField with frag_xyz their Cartesian coordinates (FRAGMENT keyword, :320-338): the box
+    becomes the fragments' bounding box + rthres, the promolecular density is evaluated (dopromol, :413) and only the
+    points between fragments survive the cutoff pass (:579-582)."""
     opts = opts or NciOptions()
-    x0, xmat, ns = nci_grid(st, nstep, opts.xinc, rthres)
-    use_promol = promol if opts.rho_void > 0 else None
+    nfrag = 0 if not fragments else len(fragments)
+    x0, xmat, ns = nci_grid(st, nstep, opts.xinc, rthres, frag_xyz if nfrag else None)
+    use_promol = promol if (opts.rho_void > 0 or nfrag > 0) else None
+    if nfrag > 0 and use_promol is None:
+        raise ValueError("NCIPLOT with fragments needs the promolecular field (dopromol, nci@proc.f90:413)")
     crho, cgrad, rhoat = field.nci(x0, xmat, ns, promol=use_promol)
+    rhofrag = gpu.nci_fragments(fragments, x0, xmat, ns) if nfrag > 0 else None
     cg = cgrad.reshape(-1).copy()
     sums, dat, ndat = gpu.nci_cutoffs(crho.reshape(-1), cg, None if rhoat is None else rhoat.reshape(-1),
                                       rhocut=opts.rhocut, dimcut=opts.dimcut, rhoplot=opts.rhoplot,
                                       srhorange=opts.srhorange, onlyneg=opts.onlyneg, rho_void=opts.rho_void,
-                                      omega=st.omega)
-    return dict(crho=crho, cgrad=cgrad, cgrad_masked=cg.reshape(cgrad.shape), rhoat=rhoat, sums=sums, dat=dat,
-                ndat=ndat, grid=(x0, xmat, ns))
+                                      omega=st.omega, rhofrag=rhofrag, rhoparam=opts.rhoparam, rhoparam2=opts.rhoparam2)
+    return dict(crho=crho, cgrad=cgrad, cgrad_masked=cg.reshape(cgrad.shape), rhoat=rhoat, rhofrag=rhofrag, sums=sums,
+                dat=dat, ndat=ndat, grid=(x0, xmat, ns))

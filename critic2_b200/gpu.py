@@ -65,6 +65,18 @@ def lib():
         L.c2gpu_nci_cutoffs_dev.argtypes = [C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                             C.c_double, dp, C.c_int, C.c_double, dp, C.POINTER(C.c_long), C.c_void_p,
                                             C.c_long, C.c_void_p]
+        L.c2gpu_nci_fragments.argtypes = [C.c_int, C.POINTER(C.c_void_p), dp, dp, ip, dp]
+        L.c2gpu_nci_fragments_dev.argtypes = [C.c_int, C.POINTER(C.c_void_p), dp, dp, ip, C.c_void_p, C.c_int, C.c_int,
+                                              C.c_void_p]
+        L.c2gpu_nci_fragments_dev_part.argtypes = [C.c_int, C.POINTER(C.c_void_p), dp, dp, ip, C.c_void_p, C.c_int,
+                                                   C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_nci_cutoffs_frag.argtypes = [C.c_long, dp, dp, dp, C.c_int, dp, C.c_double, C.c_double, C.c_double,
+                                             C.c_double, C.c_double, dp, C.c_int, C.c_double, C.c_double, dp,
+                                             C.POINTER(C.c_long), dp, C.c_long]
+        L.c2gpu_nci_cutoffs_frag_dev.argtypes = [C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                                 C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, dp,
+                                                 C.c_int, C.c_double, dp, C.POINTER(C.c_long), C.c_void_p, C.c_long,
+                                                 C.c_void_p]
         L.c2gpu_promol_grid.argtypes = [C.c_void_p, ip, dp]
         L.c2gpu_promol_grid_dev.argtypes = [C.c_void_p, ip, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_eval_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp]
@@ -303,17 +315,73 @@ class PromolField(_Field):
         return s.value
 
 
+class FragmentField(_Field):
+    """One NCIPLOT fragment (nci@proc.f90:534-550): a promolecular handle over the fragment's own atoms only -- no
+    periodic images, cutoff g%rmax (cutrad = 1e30), molecule frame with identity matrices so the point is never folded.
+    xyz: (nat, 3) Cartesian bohr (the reference's fr%at(:)%r); z: atomic numbers; tables as for PromolField."""
+
+    def __init__(self, xyz, z, tables):
+        xyz = _f64(xyz).reshape(-1, 3)
+        z = _i32(z).reshape(-1)
+        nat = xyz.shape[0]
+        zspc = np.unique(z)
+        ispc = _i32(np.searchsorted(zspc, z) + 1)
+        cidx = _i32(np.arange(1, nat + 1))
+        ngrid, aa, bb, tr, tf = [], [], [], [], []
+        for zz in zspc:
+            t = tables.get(int(zz))
+            if t is None:                      # agrid(iz) not initialised: the atom is skipped (:541)
+                ngrid.append(0); aa.append(0.0); bb.append(1.0)
+                continue
+            ngrid.append(len(t["r"])); aa.append(float(t["a"])); bb.append(float(t["b"]))
+            tr.append(_f64(t["r"])); tf.append(_f64(t["f"]))
+        cat = lambda x: np.concatenate(x) if x else np.zeros(1)
+        r_, f_ = cat(tr), cat(tf)
+        eye = np.eye(3)
+        h = C.c_void_p()
+        cut = np.full(len(zspc), 1e30)
+        _check(lib().c2gpu_promol_create(nat, nat, _d(xyz), _i(ispc), _i(cidx), len(zspc), _i(_i32(zspc)), _i(_i32(ngrid)),
+                                         _d(_f64(aa)), _d(_f64(bb)), _d(cut), _d(r_), _d(f_), _d(f_), _d(f_), 1,
+                                         _d(_colmajor(eye)), _d(_colmajor(eye)), _d(_colmajor(eye)), _d(_colmajor(eye)),
+                                         None, C.byref(h)))
+        self.handle = h
+        self.nat = nat
+
+
+def nci_fragments(frags, x0, xmat, nstep):
+    """rhofrag(k,j,i,ifr) on HOST arrays: returns (nfrag, n1, n2, n3), z fastest."""
+    x0a, xda, nna = _grid_args(x0, xmat, nstep)
+    npt = int(nna[0]) * int(nna[1]) * int(nna[2])
+    out = np.empty(len(frags) * npt)
+    hs = (C.c_void_p * len(frags))(*[f.handle for f in frags])
+    _check(lib().c2gpu_nci_fragments(len(frags), hs, _d(x0a), _d(xda), _i(nna), _d(out)))
+    return out.reshape(len(frags), nna[0], nna[1], nna[2])
+
+
+def nci_fragments_dev(frags, x0, xmat, nstep, rhofrag, part: int = 0, nparts: int = 1, layer_height: int = 8,
+                      stream: int = 0):
+    """rhofrag on a DEVICE tensor of nfrag*n1*n2*n3 doubles; interleaved x-layers like nci_dev_part."""
+    x0a, xda, nna = _grid_args(x0, xmat, nstep)
+    hs = (C.c_void_p * len(frags))(*[f.handle for f in frags])
+    _check(lib().c2gpu_nci_fragments_dev_part(len(frags), hs, _d(x0a), _d(xda), _i(nna), C.c_void_p(rhofrag.data_ptr()),
+                                              part, nparts, layer_height, C.c_void_p(stream)))
+
+
 def nci_cutoffs(crho, cgrad, rhoat=None, rhocut=0.2, dimcut=2.0, rhoplot=0.1, srhorange=(-1e30, 1e30), onlyneg=False,
-                rho_void=-1.0, omega=1.0, want_dat=True):
+                rho_void=-1.0, omega=1.0, want_dat=True, rhofrag=None, rhoparam=0.95, rhoparam2=0.75):
     """nciplot cutoff pass (nci@proc.f90:569-604) on HOST arrays; cgrad is modified in place.
-    Returns (sums[3], dat (ndat, 2))."""
+    rhofrag: None or (nfrag, npts) fragment densities (then rhoat is required, :579-582).
+    Returns (sums[3], dat (ndat, 2), ndat)."""
     npts = crho.size
     sums = np.zeros(3)
     nd = C.c_long(0)
     dat = np.zeros((npts if want_dat else 0, 2))
     sr = _f64(srhorange)
     assert crho.flags.c_contiguous and cgrad.flags.c_contiguous
-    _check(lib().c2gpu_nci_cutoffs(npts, _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None, rhocut, dimcut,
-                                   rhoplot, _d(sr), int(onlyneg), rho_void, omega, _d(sums), C.byref(nd),
-                                   _d(dat) if want_dat else None, npts if want_dat else 0))
+    nfrag = 0 if rhofrag is None else int(np.asarray(rhofrag).shape[0])
+    rf = None if rhofrag is None else _f64(rhofrag).reshape(nfrag, -1)
+    _check(lib().c2gpu_nci_cutoffs_frag(npts, _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None, nfrag,
+                                        _d(rf) if rf is not None else None, rhoparam, rhoparam2, rhocut, dimcut, rhoplot,
+                                        _d(sr), int(onlyneg), rho_void, omega, _d(sums), C.byref(nd),
+                                        _d(dat) if want_dat else None, npts if want_dat else 0))
     return sums, dat[:nd.value].copy(), nd.value

@@ -113,6 +113,29 @@ int c2gpu_nci_cutoffs_dev(long npts, const double *crho_dev, double *cgrad_dev, 
                           double rho_void, double raw_sums[3], long *ndat, double *dat_dev, long maxdat,
                           void *stream);
 
+/* ---- NCIPLOT fragments: src/nci@proc.f90:534-550 (rhofrag) and :579-582 (the `inter` test) ----------------------
+   A fragment handle is a promolecular handle made by c2gpu_promol_create over the fragment's own atoms only
+   (nenv = ncell = fr%nat, cidx = 1..nat, no periodic images), with cutrad = 1e30 for every species (the reference
+   cuts at agrid(iz)%rmax only, :542), ismolecule = 1 and identity cell matrices (the point is not folded, :538).
+   rhofrag: [nfrag][n1*n2*n3] = the reference's rhofrag(k,j,i,ifr), z fastest. */
+int c2gpu_nci_fragments(int nfrag, void *const *hfrag, const double x0[3], const double xmat[9], const int nstep[3],
+                        double *rhofrag);
+int c2gpu_nci_fragments_dev(int nfrag, void *const *hfrag, const double x0[3], const double xmat[9], const int nstep[3],
+                            double *rhofrag_dev, int i0, int i1, void *stream);
+/* the interleaved x-layers (height layer_height = c2gpu_layer_height(href)) of c2gpu_nci_grid_dev_part */
+int c2gpu_nci_fragments_dev_part(int nfrag, void *const *hfrag, const double x0[3], const double xmat[9],
+                                 const int nstep[3], double *rhofrag_dev, int part, int nparts, int layer_height,
+                                 void *stream);
+/* Cutoff pass with fragments (nfrag > 0 requires rhofrag and rhoat; defaults rhoparam 0.95, rhoparam2 0.75, :120-121) */
+int c2gpu_nci_cutoffs_frag(long npts, double *crho, double *cgrad, const double *rhoat, int nfrag, const double *rhofrag,
+                           double rhoparam, double rhoparam2, double rhocut, double dimcut, double rhoplot,
+                           const double srhorange[2], int onlyneg, double rho_void, double omega, double sums[3],
+                           long *ndat, double *dat, long maxdat);
+int c2gpu_nci_cutoffs_frag_dev(long npts, const double *crho_dev, double *cgrad_dev, const double *rhoat_dev, int nfrag,
+                               const double *rhofrag_dev, double rhoparam, double rhoparam2, double rhocut,
+                               double dimcut, double rhoplot, const double srhorange[2], int onlyneg, double rho_void,
+                               double raw_sums[3], long *ndat, double *dat_dev, long maxdat, void *stream);
+
 /* ---- whole-cell promolecular grid: crystal%promolecular_grid, src/crystalmod@proc.f90:5118-5158 --------------- */
 int c2gpu_promol_grid(void *hpromol, const int n[3], double *out);
 int c2gpu_promol_grid_dev(void *hpromol, const int n[3], double *out_dev, int iz0, int iz1, void *stream);

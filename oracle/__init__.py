@@ -63,6 +63,10 @@ def lib():
         L.orc_nci_cutoffs.restype = C.c_long
         L.orc_nci_cutoffs.argtypes = [ip, dp, dp, dp, C.c_double, C.c_double, C.c_double, dp, C.c_int, C.c_double,
                                       C.c_double, dp, dp, C.c_long]
+        L.orc_nci_fragments.argtypes = [C.c_int, ip, dp, ip, C.POINTER(C.c_void_p), dp, dp, ip, dp, C.c_int]
+        L.orc_nci_cutoffs_frag.restype = C.c_long
+        L.orc_nci_cutoffs_frag.argtypes = [ip, dp, dp, dp, C.c_int, dp, C.c_double, C.c_double, C.c_double, C.c_double,
+                                           C.c_double, dp, C.c_int, C.c_double, C.c_double, dp, dp, C.c_long]
         L.orc_promolecular_grid.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), ip, dp, C.c_int]
         L.orc_grd_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
         L.orc_nact_points.argtypes = [C.c_void_p, C.c_void_p, C.c_long, dp, C.POINTER(C.c_long), C.c_int]
@@ -246,17 +250,35 @@ class Field:
         return crho.reshape(shp), cgrad.reshape(shp), (rhoat.reshape(shp) if rhoat is not None else None)
 
 
+def nci_fragments(frags, grids: Grid1Set, x0, xmat, nstep, nthreads=0):
+    """rhofrag of nciplot (nci@proc.f90:534-550).  frags: list of (xyz (nat,3) Cartesian bohr, z (nat,)).
+    Returns (nfrag, n1, n2, n3), z fastest."""
+    nstep = _i32(nstep)
+    npt = int(nstep[0]) * int(nstep[1]) * int(nstep[2])
+    nat = _i32([len(f[1]) for f in frags])
+    xyz = _f64(np.concatenate([np.asarray(f[0], float).reshape(-1, 3) for f in frags]))
+    z = _i32(np.concatenate([np.asarray(f[1]).reshape(-1) for f in frags]))
+    out = np.zeros(len(frags) * npt)
+    lib().orc_nci_fragments(len(frags), _i(nat), _d(xyz), _i(z), grids.arr, _d(_f64(x0)), _d(_colmajor(xmat)), _i(nstep),
+                            _d(out), nthreads)
+    return out.reshape(len(frags), nstep[0], nstep[1], nstep[2])
+
+
 def nci_cutoffs(crho, cgrad, rhoat=None, rhocut=0.2, dimcut=2.0, rhoplot=0.1, srhorange=(-1e30, 1e30), onlyneg=False,
-                rho_void=-1.0, omega=1.0):
-    """nciplot cutoff pass; modifies cgrad in place. Returns (sums[3], dat (ndat,2))."""
+                rho_void=-1.0, omega=1.0, rhofrag=None, rhoparam=0.95, rhoparam2=0.75):
+    """nciplot cutoff pass; modifies cgrad in place. Returns (sums[3], dat (ndat,2)).
+    rhofrag: None or (nfrag, n1, n2, n3) fragment densities (then rhoat is required)."""
     shp = crho.shape
     nstep = _i32(shp)
     sums = np.zeros(3)
     maxdat = crho.size
     dat = np.zeros((maxdat, 2))
     sr = _f64(srhorange)
-    n = lib().orc_nci_cutoffs(_i(nstep), _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None, rhocut, dimcut,
-                              rhoplot, _d(sr), int(onlyneg), rho_void, omega, _d(sums), _d(dat), maxdat)
+    nfrag = 0 if rhofrag is None else int(rhofrag.shape[0])
+    rf = None if rhofrag is None else _f64(rhofrag)
+    n = lib().orc_nci_cutoffs_frag(_i(nstep), _d(crho), _d(cgrad), _d(rhoat) if rhoat is not None else None, nfrag,
+                                   _d(rf) if rf is not None else None, rhoparam, rhoparam2, rhocut, dimcut, rhoplot,
+                                   _d(sr), int(onlyneg), rho_void, omega, _d(sums), _d(dat), maxdat)
     return sums, dat[:n].copy()
 
 

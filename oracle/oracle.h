@@ -133,6 +133,14 @@ void orc_nci(const orc_field *fref, const orc_field *fpromol, const double *x0, 
 long orc_nci_cutoffs(const int *nstep, double *crho, double *cgrad, const double *rhoat, double rhocut, double dimcut,
                      double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega, double *sums,
                      double *dat, long maxdat);
+/* nciplot fragment densities (src/nci@proc.f90:534-550) and the cutoff pass with fragments (:579-582);
+   rhofrag is [nfrag][n1*n2*n3] */
+void orc_nci_fragments(int nfrag, const int *nat, const double *xyz, const int *z, orc_grid1 *const *agrid,
+                       const double *x0, const double *xmat, const int *nstep, double *rhofrag, int nthreads);
+long orc_nci_cutoffs_frag(const int *nstep, double *crho, double *cgrad, const double *rhoat, int nfrag,
+                          const double *rhofrag, double rhoparam, double rhoparam2, double rhocut, double dimcut,
+                          double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega,
+                          double *sums, double *dat, long maxdat);
 /* promolecular_grid (src/crystalmod@proc.f90:5118-5158): whole-cell grid at fractional nodes (i-1)/n, nder=0 */
 void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, double *out, int nthreads);
 /* evaluate grd on an arbitrary list of points: res is npts*ORC_RES_LEN */

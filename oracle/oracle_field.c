@@ -294,15 +294,61 @@ void orc_nci(const orc_field *fref, const orc_field *fpromol, const double *x0, 
       }
 }
 
-/* nciplot cutoff pass :569-604 (nfrag = 0) */
-long orc_nci_cutoffs(const int *nstep, double *crho, double *cgrad, const double *rhoat, double rhocut, double dimcut,
-                     double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega, double *sums,
-                     double *dat, long maxdat) {
+/* nciplot fragment densities :534-550: plain sums over the fragment's own atoms (no periodic images, the point is
+   not folded), cutoff g%rmax only.  xyz/z: the atoms of all fragments back to back (nat[ifr] each), Cartesian.
+   rhofrag: [nfrag][n1*n2*n3], each (k,j,i) with k fastest. */
+void orc_nci_fragments(int nfrag, const int *nat, const double *xyz, const int *z, orc_grid1 *const *agrid,
+                       const double *x0, const double *xmat, const int *nstep, double *rhofrag, int nthreads) {
+  const size_t npt = (size_t)nstep[0] * nstep[1] * nstep[2];
+#ifdef _OPENMP
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic)
+  for (int i = 0; i < nstep[0]; i++)
+    for (int j = 0; j < nstep[1]; j++)
+      for (int k = 0; k < nstep[2]; k++) {
+        double x[3];
+        for (int d = 0; d < 3; d++) x[d] = x0[d] + i * xmat[d] + j * xmat[3 + d] + k * xmat[6 + d]; /* :504 */
+        size_t idx = (size_t)k + (size_t)nstep[2] * ((size_t)j + (size_t)nstep[1] * i);
+        size_t a0 = 0;
+        for (int ifr = 0; ifr < nfrag; ifr++) {
+          double sum = 0.0;                                       /* :535 */
+          for (int ia = 0; ia < nat[ifr]; ia++) {
+            const double *r = xyz + 3 * (a0 + ia);
+            double xd[3] = {x[0] - r[0], x[1] - r[1], x[2] - r[2]};
+            double dist = orc_norm2(xd, 3);                       /* :539 */
+            int iz = z[a0 + ia];
+            if (iz < 1 || iz > 118 || !agrid[iz] || !agrid[iz]->isinit) continue; /* :541 */
+            if (dist > agrid[iz]->rmax) continue;                 /* :542 */
+            dist = fmax(dist, agrid[iz]->r[0]);                   /* :543 */
+            dist = fmax(dist, 1e-14);                             /* :544 */
+            double rrho, rrho1, rrho2;
+            orc_grid1_interp(agrid[iz], dist, &rrho, &rrho1, &rrho2);
+            rrho = fmax(rrho, 0.0);                               /* :546 */
+            sum += rrho;
+          }
+          rhofrag[(size_t)ifr * npt + idx] = sum;
+          a0 += nat[ifr];
+        }
+      }
+}
+
+/* nciplot cutoff pass :569-604.  nfrag > 0: rhofrag [nfrag][npts] and rhoat are required (:579-582). */
+long orc_nci_cutoffs_frag(const int *nstep, double *crho, double *cgrad, const double *rhoat, int nfrag,
+                          const double *rhofrag, double rhoparam, double rhoparam2, double rhocut, double dimcut,
+                          double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega,
+                          double *sums, double *dat, long maxdat) {
   double sumq = 0, sumqp = 0, sumv = 0;
   long ndat = 0;
   size_t ntot = (size_t)nstep[0] * nstep[1] * nstep[2];
   for (size_t idx = 0; idx < ntot; idx++) { /* (i,j,k) order with k fastest == linear order of the arrays */
     int inter = 1;
+    if (nfrag > 0) {                                              /* :579-582 */
+      double s = 0.0;
+      for (int ifr = 0; ifr < nfrag; ifr++) s += rhofrag[(size_t)ifr * ntot + idx];
+      inter = s >= rhoparam2 * rhoat[idx];
+      for (int ifr = 0; ifr < nfrag; ifr++) inter = inter && (rhofrag[(size_t)ifr * ntot + idx] <= s * rhoparam);
+    }
     if (rho_void > 0) {
       inter = inter && (rhoat[idx] < rho_void);
       if (rhoat[idx] < rho_void) {
@@ -324,6 +370,13 @@ long orc_nci_cutoffs(const int *nstep, double *crho, double *cgrad, const double
   sums[1] = sumqp * omega / nt;
   sums[2] = sumv * omega / nt;
   return ndat;
+}
+
+long orc_nci_cutoffs(const int *nstep, double *crho, double *cgrad, const double *rhoat, double rhocut, double dimcut,
+                     double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega, double *sums,
+                     double *dat, long maxdat) {
+  return orc_nci_cutoffs_frag(nstep, crho, cgrad, rhoat, 0, NULL, 0.95, 0.75, rhocut, dimcut, rhoplot, srhorange, onlyneg,
+                              rho_void, omega, sums, dat, maxdat);
 }
 
 /* promolecular_grid crystalmod@proc.f90:5118-5158 */

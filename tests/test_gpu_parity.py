@@ -187,6 +187,50 @@ def test_nci_void_with_promolecular(G, O):
     assert np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
 
 
+def test_nci_fragments(G, O):
+    """NCIPLOT with two fragments (FRAGMENT keyword): box from the fragments (:350-368), rhofrag (:534-550) and the
+    `inter` classification (:579-582), host entry points and the interleaved device layers."""
+    import torch
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    tabs = cases.tables()
+    order = np.argsort(st.r[:, 0], kind="stable")
+    ia, ib = order[:6], order[6:]
+    frag_xyz = [st.r[ia], st.r[ib]]
+    frag_z = [f.z[ia], f.z[ib]]
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(18, 17, 16), frag_xyz=frag_xyz)
+    lo = np.concatenate(frag_xyz).min(0) - 2.0
+    np.testing.assert_allclose(x0, lo, rtol=0, atol=1e-12)
+    env = O.Environ(st)
+    of = O.Field(env, wfn=O.Wfn(f))
+    grids = O.Grid1Set(tabs)
+    op = O.Field(env, grids=grids)
+    rrho, rgrad, rat = of.nci(x0, xmat, ns, promol=op)
+    rfr = O.nci_fragments(list(zip(frag_xyz, frag_z)), grids, x0, xmat, ns)
+    fld, pro = G.WfnField(f, st), G.PromolField(st, tabs)
+    frs = [G.FragmentField(r, z, tabs) for r, z in zip(frag_xyz, frag_z)]
+    opts = drivers.NciOptions(rhoparam=0.9, rhoparam2=0.8)
+    out = drivers.nciplot(fld, st, nstep=(18, 17, 16), opts=opts, promol=pro, fragments=frs, frag_xyz=frag_xyz)
+    assert _nci_compare(out["crho"], out["cgrad"], rrho, rgrad) == 0
+    check_rho(out["rhoat"], rat, "rhoat")
+    check_rho(out["rhofrag"], rfr, "rhofrag")
+    rg = rgrad.copy()
+    rsums, rdat = O.nci_cutoffs(rrho.copy(), rg, rat, rhofrag=rfr, rhoparam=0.9, rhoparam2=0.8, omega=st.omega)
+    assert 0 < len(rdat) < rrho.size
+    assert out["ndat"] == len(rdat)
+    assert np.array_equal(out["cgrad_masked"] == 100.0, rg == 100.0)
+    np.testing.assert_allclose(out["dat"][:, 0], rdat[:, 0], rtol=1e-10, atol=0)
+    # device entry: two interleaved parts fill disjoint x-layers and together reproduce the host result
+    npt = int(np.prod(ns))
+    dev = torch.zeros(2 * npt, dtype=torch.float64, device="cuda")
+    lh = fld.layer_height()
+    for part in range(2):
+        G.nci_fragments_dev(frs, x0, xmat, ns, dev, part=part, nparts=2, layer_height=lh)
+    torch.cuda.synchronize()
+    assert np.array_equal(dev.cpu().numpy().reshape(out["rhofrag"].shape), out["rhofrag"])
+
+
 def test_promolecular_quartz_cube(G, O):
     """Promolecular density of alpha-quartz (periodic, images) with gradient and Hessian on a ragged whole-cell grid."""
     from critic2_b200 import drivers

@@ -211,6 +211,46 @@ def test_nci_cutoffs_against_numpy():
     assert np.array_equal(cg == 100.0, mask | (cgrad == 100.0))
 
 
+def test_nci_fragment_density_and_inter_test():
+    """rhofrag (nci@proc.f90:534-550) against the radial table itself, and the fragment `inter` test (:579-582)."""
+    tabs = cases.tables()
+    grids = oracle.Grid1Set(tabs)
+    # one O atom at the origin, one H atom on the x axis: fragments = the single atoms
+    frags = [(np.array([[0.0, 0.0, 0.0]]), np.array([8])), (np.array([[3.0, 0.0, 0.0]]), np.array([1]))]
+    x0 = np.array([-4.0, 0.2, -0.1])
+    xmat = np.diag([0.5, 0.25, 0.125])
+    ns = (30, 3, 2)
+    rf = oracle.nci_fragments(frags, grids, x0, xmat, ns)
+    assert rf.shape == (2, 30, 3, 2)
+    for (i, j, k) in ((0, 0, 0), (7, 2, 1), (13, 1, 0), (29, 2, 1)):
+        x = x0 + xmat @ np.array([i, j, k], float)
+        for ifr, (r, z) in enumerate(frags):
+            d = np.linalg.norm(x - r[0])
+            t = tabs[int(z[0])]
+            want = 0.0 if d > t["r"][-1] else max(grids.interp(int(z[0]), max(d, t["r"][0]))[0], 0.0)
+            assert rf[ifr, i, j, k] == pytest.approx(want, rel=1e-13, abs=0)
+    # beyond rmax of both species the fragment densities vanish exactly (:542)
+    far = oracle.nci_fragments(frags, grids, np.array([40.0, 0, 0]), xmat, (2, 2, 2))
+    assert np.all(far == 0.0)
+    # cutoff pass: a point survives only if the fragments together hold >= rhoparam2 of rhoat and none holds > rhoparam
+    rng = np.random.default_rng(3)
+    shp = (6, 5, 4)
+    crho = rng.normal(0, 5, shp)
+    cgrad = np.abs(rng.normal(0, 0.5, shp))
+    f1, f2 = np.abs(rng.normal(0.02, 0.02, shp)), np.abs(rng.normal(0.02, 0.02, shp))
+    rhoat = (f1 + f2) * rng.uniform(0.9, 1.6, shp)
+    cg = cgrad.copy()
+    sums, dat = oracle.nci_cutoffs(crho, cg, rhoat, rhofrag=np.stack([f1, f2]), rhoparam=0.9, rhoparam2=0.8)
+    s = f1 + f2
+    inter = (s >= 0.8 * rhoat) & (f1 <= 0.9 * s) & (f2 <= 0.9 * s)
+    assert 0 < inter.sum() < inter.size
+    isdat = (np.abs(crho) < 20) & (cgrad < 2.0) & inter
+    assert len(dat) == isdat.sum()
+    np.testing.assert_allclose(dat[:, 1], cgrad[isdat])
+    assert np.array_equal(cg == 100.0, (np.abs(crho) > 10) | ~inter)
+    assert np.all(sums == 0.0)      # no VOID: the void sums stay zero
+
+
 def test_cube_loop_matches_point_calls_and_layout():
     f = cases.golden_wfn("h2o-wfx")
     st = cases.mol_structure(f)
