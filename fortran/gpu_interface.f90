@@ -95,6 +95,27 @@ module gpu_interface
        integer(c_long) :: ndat
        integer(c_int) :: ierr
      end function c2gpu_nci_cutoffs
+     function c2gpu_nci_fragments(nfrag,hfrag,x0,xmat,nstep,rhofrag) bind(c,name="c2gpu_nci_fragments") result(ierr)
+       import :: c_int, c_double, c_ptr
+       integer(c_int), value :: nfrag
+       type(c_ptr) :: hfrag(*)
+       real(c_double) :: x0(3), xmat(3,3)
+       integer(c_int) :: nstep(3)
+       real(c_double) :: rhofrag(*)
+       integer(c_int) :: ierr
+     end function c2gpu_nci_fragments
+     function c2gpu_nci_cutoffs_frag(npts,crho,cgrad,rhoat,nfrag,rhofrag,rhoparam,rhoparam2,rhocut,dimcut,rhoplot,&
+        srhorange,onlyneg,rho_void,omega,sums,ndat,dat,maxdat) bind(c,name="c2gpu_nci_cutoffs_frag") result(ierr)
+       import :: c_int, c_long, c_double, c_ptr
+       integer(c_long), value :: npts, maxdat
+       real(c_double) :: crho(*), cgrad(*)
+       type(c_ptr), value :: rhoat, rhofrag, dat
+       integer(c_int), value :: nfrag, onlyneg
+       real(c_double), value :: rhoparam, rhoparam2, rhocut, dimcut, rhoplot, rho_void, omega
+       real(c_double) :: srhorange(2), sums(3)
+       integer(c_long) :: ndat
+       integer(c_int) :: ierr
+     end function c2gpu_nci_cutoffs_frag
      function c2gpu_promol_grid(h,n,out) bind(c,name="c2gpu_promol_grid") result(ierr)
        import :: c_int, c_double, c_ptr
        type(c_ptr), value :: h
@@ -307,6 +328,102 @@ contains
     sumq = sums(1); sumqp = sums(2); sumv = sums(3)
     ok = (ierr == 0)
   end subroutine gpu_nci_cutoffs
+
+  !> Device image of one NCIPLOT fragment (nci@proc.f90:534-550): the fragment's own atoms, cutoff agrid(iz)%rmax only
+  !> (cutrad = 1e30), molecule frame with identity matrices so that the point is used as is (:538).
+  function gpu_fragment_handle(fr) result(h)
+    use fragmentmod, only: fragment
+    use grid1mod, only: agrid
+    use param, only: maxzat
+    type(fragment), intent(in) :: fr
+    type(c_ptr) :: h
+    real(c_double), allocatable :: xyz(:,:), a(:), b(:), cut(:), tr(:), tf(:)
+    integer(c_int), allocatable :: ispc(:), cidx(:), zspc(:), ngrid(:)
+    real(c_double) :: eye(3,3)
+    integer :: i, is, iz, ntot, n0
+    integer(c_int) :: ierr
+    h = c_null_ptr
+    if (fr%nat == 0) return
+    eye = 0d0
+    do i = 1, 3
+       eye(i,i) = 1d0
+    end do
+    allocate(xyz(3,fr%nat),ispc(fr%nat),cidx(fr%nat))
+    do i = 1, fr%nat
+       xyz(:,i) = fr%at(i)%r
+       ispc(i) = fr%at(i)%is
+       cidx(i) = i
+    end do
+    allocate(zspc(fr%nspc),ngrid(fr%nspc),a(fr%nspc),b(fr%nspc),cut(fr%nspc))
+    cut = 1d30
+    ntot = 0
+    do is = 1, fr%nspc
+       iz = fr%spc(is)%z
+       zspc(is) = iz
+       ngrid(is) = 0; a(is) = 0d0; b(is) = 1d0
+       if (iz > 0 .and. iz <= maxzat) then
+          if (agrid(iz)%isinit) then
+             ngrid(is) = agrid(iz)%ngrid; a(is) = agrid(iz)%a; b(is) = agrid(iz)%b
+          end if
+       end if
+       ntot = ntot + ngrid(is)
+    end do
+    allocate(tr(max(ntot,1)),tf(max(ntot,1)))
+    n0 = 0
+    do is = 1, fr%nspc
+       if (ngrid(is) == 0) cycle
+       iz = zspc(is)
+       tr(n0+1:n0+ngrid(is)) = agrid(iz)%r(1:ngrid(is))
+       tf(n0+1:n0+ngrid(is)) = agrid(iz)%f(1:ngrid(is))
+       n0 = n0 + ngrid(is)
+    end do
+    ! only the value table is read (nder = 0): f stands in for fp and fpp
+    ierr = c2gpu_promol_create(int(fr%nat,c_int),int(fr%nat,c_int),xyz,ispc,cidx,int(fr%nspc,c_int),zspc,ngrid,&
+       a,b,cut,tr,tf,tf,tf,1_c_int,eye,eye,eye,eye,c_null_ptr,h)
+    if (ierr == -1) h = c_null_ptr
+    call gpu_check("gpu_fragment_handle",ierr)
+  end function gpu_fragment_handle
+
+  !> Replacement of the fragment part of the nciplot loop (:534-550, :556): rhofrag(0:n3-1,0:n2-1,0:n1-1,nfrag).
+  subroutine gpu_nci_fragments(hfrag,x0,xmat,nstep,rhofrag,ok)
+    type(c_ptr), intent(in) :: hfrag(:)
+    real(c_double), intent(in) :: x0(3), xmat(3,3)
+    integer, intent(in) :: nstep(3)
+    real(c_double), intent(inout) :: rhofrag(0:,0:,0:,1:)
+    logical, intent(out) :: ok
+    integer(c_int) :: ierr, n(3)
+    type(c_ptr) :: hh(size(hfrag))
+    ok = .false.
+    if (.not.gpu_enabled) return
+    n = int(nstep,c_int)
+    hh = hfrag
+    ierr = c2gpu_nci_fragments(int(size(hfrag),c_int),hh,x0,xmat,n,rhofrag)
+    call gpu_check("nciplot",ierr)
+    ok = (ierr == 0)
+  end subroutine gpu_nci_fragments
+
+  !> Cutoff pass with fragments (nci@proc.f90:569-604 incl. the inter test :579-582).
+  subroutine gpu_nci_cutoffs_frag(crho,cgrad,rhoat,rhofrag,rhoparam,rhoparam2,rhocut,dimcut,rhoplot,srhorange,&
+     onlyneg,rho_void,omega,sumq,sumqp,sumv,ndat,dat,ok)
+    real(c_double), intent(inout) :: crho(0:,0:,0:), cgrad(0:,0:,0:)
+    real(c_double), intent(in), target :: rhoat(0:,0:,0:), rhofrag(0:,0:,0:,1:)
+    real(c_double), intent(in) :: rhoparam, rhoparam2, rhocut, dimcut, rhoplot, srhorange(2), rho_void, omega
+    logical, intent(in) :: onlyneg
+    real(c_double), intent(out) :: sumq, sumqp, sumv
+    integer(c_long), intent(out) :: ndat
+    real(c_double), intent(inout), target :: dat(:,:)
+    logical, intent(out) :: ok
+    real(c_double) :: sums(3)
+    integer(c_int) :: ierr
+    ok = .false.
+    if (.not.gpu_enabled) return
+    ierr = c2gpu_nci_cutoffs_frag(int(size(crho),c_long),crho,cgrad,c_loc(rhoat(0,0,0)),int(size(rhofrag,4),c_int),&
+       c_loc(rhofrag(0,0,0,1)),rhoparam,rhoparam2,rhocut,dimcut,rhoplot,srhorange,merge(1_c_int,0_c_int,onlyneg),&
+       rho_void,omega,sums,ndat,c_loc(dat(1,1)),int(size(dat,2),c_long))
+    call gpu_check("nciplot",ierr)
+    sumq = sums(1); sumqp = sums(2); sumv = sums(3)
+    ok = (ierr == 0)
+  end subroutine gpu_nci_cutoffs_frag
 
   !> Replacement of the promolecular_grid loop (crystalmod@proc.f90:5143-5158): f(n1,n2,n3), nder = 0.
   subroutine gpu_promolecular_grid(h,n,f,ok)
