@@ -310,6 +310,8 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
     int n = ngrid[s];
     d.off = (int)nodes.size(); d.n = n; d.z = zspc[s]; d.pad = 0;
     d.a = a[s]; d.b = b[s]; d.cutrad = cutrad[s];
+    d.ln2_b = b[s] != 0.0 ? std::log(2.0) / b[s] : 0.0;
+    d.lna_b = (b[s] != 0.0 && a[s] > 0.0) ? std::log(a[s]) / b[s] : 0.0;
     if (n >= 4) {
       const double *r = tab_r + off_in;
       d.rmax = r[n - 1]; d.r1 = r[0];

@@ -22,6 +22,7 @@ struct SpcDev {
   double rcut;        // min(cutrad(z), rmax) (:1246-1263); cutrad alone if the table is missing
   double cutrad;
   double rmax, r1;    // last and first node radius
+  double ln2_b, lna_b;   // ln(2)/b and ln(a)/b: the pre-screen of the log-grid index (radial_interp)
 };
 
 struct PromolDev {
@@ -63,7 +64,20 @@ __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &
   int ir;
   double r;
   if (r0 <= s.r1) { ir = 1; r = s.r1; }                                // :103-105
-  else { ir = 1 + (int)floor(__ddiv_rn(log(__ddiv_rn(r0, s.a)), s.b)); r = r0; }   // :107
+  else {                                                               // ir = 1 + floor(log(r0/a)/b), :107
+    // The FP64 log and the two divisions cost ~55 FP64 instructions per (point, atom) pair.  t = log(r0/a)/b is first
+    // estimated as ((e + log2(m)) ln2 - ln a)/b with the mantissa's log2 from the SFU (absolute error <= 2^-22 on
+    // [1,2] -> |dt| < 1.3e-4 for b = 0.002); unless t lies within 4e-4 of an integer its floor is already certain,
+    // otherwise (0.08 % of the pairs) the reference's own expression decides.  The index is identical either way.
+    const long long bits = __double_as_longlong(r0);
+    const int e = (int)((bits >> 52) & 0x7ff) - 1023;
+    const double mant = __longlong_as_double((bits & 0x000fffffffffffffll) | 0x3ff0000000000000ll);
+    const double t = fma((double)e + (double)__log2f((float)mant), s.ln2_b, -s.lna_b);
+    const double ft = floor(t), fr = t - ft;
+    if (fr > 4e-4 && fr < 1.0 - 4e-4 && s.b >= 1e-3) ir = 1 + (int)ft;
+    else ir = 1 + (int)floor(__ddiv_rn(log(__ddiv_rn(r0, s.a)), s.b));
+    r = r0;
+  }
   int base = min(max(ir, 2), s.n - 2) - 2;                             // :110, 0-based first node
   const double4 *nd = m.nodes + s.off + base;
   const double4 n0 = nd[0], n1 = nd[1], n2 = nd[2], n3 = nd[3];
@@ -83,12 +97,15 @@ __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &
 
 constexpr int PROMOL_PT = 256;    // points per tile = threads per CTA
 constexpr int PROMOL_CAP = 768;   // shared-memory atom list capacity (>= 2*PROMOL_PT)
+constexpr int PROMOL_NSPC = 8;    // species whose constants are staged in shared memory
 
 template <int ND>
-__global__ void __launch_bounds__(PROMOL_PT) promol_grid_kernel(const __grid_constant__ PromolParams p) {
+__global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel(const __grid_constant__ PromolParams p) {
   constexpr int NT = PROMOL_PT, NW = NT / 32;
   __shared__ double4 s_atom[PROMOL_CAP];
-  __shared__ int s_cnt[NW];
+  __shared__ double s_rc2[PROMOL_CAP];       // squared cutoff of the candidate's species
+  __shared__ SpcDev s_spc[PROMOL_NSPC];      // species constants (global memory beyond PROMOL_NSPC species)
+  __shared__ int s_cnt[NW], s_rowoff[NT], s_rowi0[NT];
   __shared__ double s_red[NW * 6];
   __shared__ double s_bb[6];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -100,6 +117,11 @@ __global__ void __launch_bounds__(PROMOL_PT) promol_grid_kernel(const __grid_con
   const int a = ta0 + tid % g.ta, b = tb0 + (tid / g.ta) % g.tb, c = tc0 + tid / (g.ta * g.tb);
   const bool valid = a < na && b < nb && c < g.c1;
 
+  const SpcDev *spc = m.spc;
+  if (m.nspc <= PROMOL_NSPC) {               // visible after the barriers of the bounding-box reduction below
+    if (tid < m.nspc) s_spc[tid] = m.spc[tid];
+    spc = s_spc;
+  }
   double xc[3] = {0, 0, 0};
   double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
   if (valid) {
@@ -151,19 +173,24 @@ __global__ void __launch_bounds__(PROMOL_PT) promol_grid_kernel(const __grid_con
     if (valid) {
       for (int i = 0; i < nlist; i++) {
         const double4 at = s_atom[i];
-        int is, cidx;
-        unpack_atom(at, is, cidx);
-        const SpcDev s = m.spc[is];
         // the reference takes at%r - x0 for the distance (:988) and xc - at%r for the gradient (:1308)
         const double ex = at.x - xc[0], ey = at.y - xc[1], ez = at.z - xc[2];
         const double d2 = ex * ex + ey * ey + ez * ez;
         isnuc = isnuc || d2 < 1e-10;                                 // src/environmod@proc.f90:677
-        if (!within_cut(ex, ey, ez, d2, s.rcut, s.rcut * s.rcut)) continue;   // :998
+        const double rc2 = s_rc2[i];
+        if (d2 > rc2 * (1.0 + 1e-14)) continue;                      // :998, outside for certain
+        int is, cidx;
+        unpack_atom(at, is, cidx);
+        const SpcDev &s = spc[is];
+        if (d2 >= rc2 * (1.0 - 1e-14) && norm2_ref(ex, ey, ez) > s.rcut) continue;   // rounding band: the reference's norm2
         if (s.n == 0) continue;                                      // :1298-1299
         if (m.fragmask && !m.fragmask[cidx]) continue;               // :1287-1290
         npair++;
-        double r = norm2_ref(ex, ey, ez);
-        if (r > s.cutrad) continue;                                  // :1295
+        // dist (:988, gfortran norm2) = sqrt(d2) to ~2 ulp, which moves rho by ~1e-13 relative; only at the table end,
+        // where interp switches to exactly 0 (:98), is the reference's own scaled arithmetic replayed.  The test
+        // r > cutrad (:1295) cannot fire here: r <= rcut = min(cutrad, rmax).
+        double r = __dsqrt_rn(d2);
+        if (r > s.rmax * (1.0 - 1e-14)) r = norm2_ref(ex, ey, ez);
         r = fmax(fmax(r, s.r1), 1e-14);                              // :1302
         double rho, rhop, rhopp;
         radial_interp<ND>(m, s, r, rho, rhop, rhopp);
@@ -190,35 +217,74 @@ __global__ void __launch_bounds__(PROMOL_PT) promol_grid_kernel(const __grid_con
     nlist = 0;
   };
 
-  for (int bz = blo[2]; bz <= bhi[2]; bz++)
-    for (int by = blo[1]; by <= bhi[1]; by++) {
-      const int rowbase = (bz * m.nbin[1] + by) * m.nbin[0];
-      const int i0 = m.bin_start[rowbase + blo[0]], i1 = m.bin_start[rowbase + bhi[0] + 1];
-      for (int base = i0; base < i1; base += NT) {
-        const int i = base + tid;
-        bool act = false;
-        double4 at;
-        if (i < i1) {
-          at = m.atoms[i];
-          int is, cidx;
-          unpack_atom(at, is, cidx);
-          const double rc = m.spc[is].rcut;
-          act = box_d2(s_bb, at.x, at.y, at.z) <= rc * rc * (1.0 + 1e-12) + 1e-9;
-        }
-        const unsigned mk = __ballot_sync(~0u, act);
-        if (lane == 0) s_cnt[warp] = __popc(mk);
-        __syncthreads();
-        int off = nlist, tot = 0;
-#pragma unroll
-        for (int w = 0; w < NW; w++) {
-          if (w < warp) off += s_cnt[w];
-          tot += s_cnt[w];
-        }
-        if (act) s_atom[off + __popc(mk & ((1u << lane) - 1u))] = at;
-        nlist += tot;
-        if (nlist > PROMOL_CAP - NT) flush(); else __syncthreads();
-      }
+  // Candidate scan.  The atoms of a (bz, by) bin row with bx in [blo, bhi] are contiguous in `atoms`; the rows are
+  // flattened into one virtual index space (prefix sums of the row lengths, NT rows at a time) so the block tests NT
+  // candidates per pass instead of one short row per pass (a row holds ~10-30 atoms: two block barriers each).
+  const int nby = bhi[1] - blo[1] + 1, nrow = nby * (bhi[2] - blo[2] + 1);
+  for (int r0 = 0; r0 < nrow; r0 += NT) {
+    const int r = r0 + tid;
+    int i0 = 0, len = 0;
+    if (r < nrow) {
+      const int rowbase = ((blo[2] + r / nby) * m.nbin[1] + blo[1] + r % nby) * m.nbin[0];
+      i0 = m.bin_start[rowbase + blo[0]];
+      len = m.bin_start[rowbase + bhi[0] + 1] - i0;
     }
+    int incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(~0u, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_cnt[warp] = incl;
+    __syncthreads();
+    int woff = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+      if (w < warp) woff += s_cnt[w];
+      total += s_cnt[w];
+    }
+    s_rowoff[tid] = woff + incl - len;      // exclusive prefix: first virtual index of this row
+    s_rowi0[tid] = i0;
+    __syncthreads();
+    const int nr = min(NT, nrow - r0);
+    for (int base = 0; base < total; base += NT) {
+      const int v = base + tid;
+      bool act = false;
+      double4 at;
+      double rc2 = 0.0;
+      if (v < total) {
+        int lo_r = 0, hi_r = nr - 1;        // last row with rowoff <= v
+        while (lo_r < hi_r) {
+          const int mid = (lo_r + hi_r + 1) >> 1;
+          if (s_rowoff[mid] <= v) lo_r = mid; else hi_r = mid - 1;
+        }
+        at = m.atoms[s_rowi0[lo_r] + (v - s_rowoff[lo_r])];
+        int is, cidx;
+        unpack_atom(at, is, cidx);
+        rc2 = spc[is].rcut;
+        rc2 *= rc2;
+        act = box_d2(s_bb, at.x, at.y, at.z) <= rc2 * (1.0 + 1e-12) + 1e-9;
+      }
+      const unsigned mk = __ballot_sync(~0u, act);
+      __syncthreads();                      // s_cnt of the previous pass / the prefix sums has been read by everyone
+      if (lane == 0) s_cnt[warp] = __popc(mk);
+      __syncthreads();
+      int off = nlist, tot = 0;
+#pragma unroll
+      for (int w = 0; w < NW; w++) {
+        if (w < warp) off += s_cnt[w];
+        tot += s_cnt[w];
+      }
+      if (act) {
+        const int slot = off + __popc(mk & ((1u << lane) - 1u));
+        s_atom[slot] = at;
+        s_rc2[slot] = rc2;
+      }
+      nlist += tot;
+      if (nlist > PROMOL_CAP - NT) flush();
+    }
+    __syncthreads();
+  }
   flush();
   if (p.count) {
 #pragma unroll
