@@ -19,6 +19,7 @@ namespace {
 thread_local std::string g_err;
 std::vector<int> g_devs;
 int g_force_cfg = -1;
+int g_fmt_force_exact = 0;
 int g_super = 8;
 
 int fail(int code, const std::string &msg) {
@@ -145,6 +146,7 @@ int c2gpu_set_option(const char *name, int value) {
   if (!name) return 1;
   if (!strcmp(name, "wfn_cfg")) { g_force_cfg = value; return 0; }
   if (!strcmp(name, "super")) { if (value < 4 || value % 4) return 1; g_super = value; return 0; }
+  if (!strcmp(name, "fmt_force_exact")) { g_fmt_force_exact = value; return 0; }   // tests: big-integer rounding path
   return 1;
 }
 

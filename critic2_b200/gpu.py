@@ -77,6 +77,13 @@ def lib():
                                                  C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, dp,
                                                  C.c_int, C.c_double, dp, C.POINTER(C.c_long), C.c_void_p, C.c_long,
                                                  C.c_void_p]
+        L.c2gpu_cube_text_size.restype = C.c_long
+        L.c2gpu_cube_text_size.argtypes = [ip, C.c_int]
+        L.c2gpu_cube_text.argtypes = [dp, ip, C.c_int, C.c_int, C.c_char_p]
+        L.c2gpu_cube_text_dev.argtypes = [C.c_void_p, ip, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.c2gpu_dat_text_size.restype = C.c_long
+        L.c2gpu_dat_text_size.argtypes = [C.c_long]
+        L.c2gpu_dat_text.argtypes = [C.c_long, dp, C.c_char_p]
         L.c2gpu_promol_grid.argtypes = [C.c_void_p, ip, dp]
         L.c2gpu_promol_grid_dev.argtypes = [C.c_void_p, ip, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_eval_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp]
@@ -385,3 +392,41 @@ def nci_cutoffs(crho, cgrad, rhoat=None, rhocut=0.2, dimcut=2.0, rhoplot=0.1, sr
                                         _d(sr), int(onlyneg), rho_void, omega, _d(sums), C.byref(nd),
                                         _d(dat) if want_dat else None, npts if want_dat else 0))
     return sums, dat[:nd.value].copy(), nd.value
+
+
+# -- text bodies of the output files: writegrid_cube (crystalmod@proc.f90:5026-5036), write_cube_body (nci@proc.f90:867-883)
+FMT_PRECISE, FMT_CUBE, FMT_NCI = 0, 1, 2
+
+
+def cube_text(g, fmt: int = FMT_PRECISE, order: int = 0) -> bytes:
+    """Formatted body of a cube file from a HOST array.  order 0: g indexed [iz][iy][ix] (lf(ix,iy,iz), x fastest),
+    records over (ix, iy) as writegrid_cube; order 1: g indexed [i][j][k] (crho(k,j,i), z fastest), records over (i, j)
+    as write_cube_body.  fmt: FMT_PRECISE '(6(1x,e22.14))', FMT_CUBE '(1p,6(1x,e12.5))', FMT_NCI '(6(1x,1p,e13.5e3))'."""
+    g = _f64(g)
+    assert g.ndim == 3
+    n = _i32(g.shape[::-1] if order == 0 else g.shape)
+    nb = lib().c2gpu_cube_text_size(_i(n), fmt)
+    buf = C.create_string_buffer(nb)
+    _check(lib().c2gpu_cube_text(_d(g), _i(n), fmt, order, buf))
+    return buf.raw
+
+
+def cube_text_dev(g, n, text, fmt: int = FMT_PRECISE, order: int = 0, stream: int = 0):
+    """DEVICE version: g a CUDA float64 tensor, text a CUDA uint8 tensor of cube_text_size(n, fmt) bytes."""
+    na = _i32(n)
+    _check(lib().c2gpu_cube_text_dev(C.c_void_p(g.data_ptr()), _i(na), fmt, order, C.c_void_p(text.data_ptr()),
+                                     C.c_void_p(stream)))
+
+
+def cube_text_size(n, fmt: int = FMT_PRECISE) -> int:
+    return int(lib().c2gpu_cube_text_size(_i(_i32(n)), fmt))
+
+
+def dat_text(pairs) -> bytes:
+    """'(1p,E15.7,E15.7)' lines of the NCIPLOT .dat file (nci@proc.f90:593-595) from (ndat, 2) pairs."""
+    p = _f64(pairs).reshape(-1, 2)
+    if p.shape[0] == 0:
+        return b""
+    buf = C.create_string_buffer(int(lib().c2gpu_dat_text_size(p.shape[0])))
+    _check(lib().c2gpu_dat_text(p.shape[0], _d(p), buf))
+    return buf.raw

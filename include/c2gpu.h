@@ -136,6 +136,21 @@ int c2gpu_nci_cutoffs_frag_dev(long npts, const double *crho_dev, double *cgrad_
                                double dimcut, double rhoplot, const double srhorange[2], int onlyneg, double rho_void,
                                double raw_sums[3], long *ndat, double *dat_dev, long maxdat, void *stream);
 
+/* ---- text bodies of the output files: the formatted writes that follow the evaluation ----
+   writegrid_cube src/crystalmod@proc.f90:5026-5036, write_cube_body src/nci@proc.f90:867-883, .dat src/nci@proc.f90:593-595.
+   fmt   0 '(6(1x,e22.14))' (PRECISECUBE, global@proc.f90:90)   1 '(1p,6(1x,e12.5))'   2 '(6(1x,1p,e13.5e3))' (NCIPLOT)
+   order 0 g(n1,n2,n3) x fastest (lf of rhoplot_cube): one record per (ix,iy), iz running   -- writegrid_cube
+         1 c(0:n3-1,0:n2-1,0:n1-1) z fastest (crho/cgrad): one record per (i,j), k running  -- write_cube_body
+   The text is exactly what the Fortran formatted write produces (6 fields per line, a new line at the end of every
+   record, round-half-even decimal conversion); the caller writes it after the header with stream access. */
+long c2gpu_cube_text_size(const int n[3], int fmt);
+int c2gpu_cube_text(const double *g, const int n[3], int fmt, int order, char *text);
+int c2gpu_cube_text_dev(const double *g_dev, const int n[3], int fmt, int order, char *text_dev /*16-byte aligned*/,
+                        void *stream);
+/* '(1p,E15.7,E15.7)' lines of the .dat file from the (rho,s) pairs of c2gpu_nci_cutoffs: 31 bytes per pair */
+long c2gpu_dat_text_size(long npairs);
+int c2gpu_dat_text(long npairs, const double *dat, char *text);
+
 /* ---- whole-cell promolecular grid: crystal%promolecular_grid, src/crystalmod@proc.f90:5118-5158 --------------- */
 int c2gpu_promol_grid(void *hpromol, const int n[3], double *out);
 int c2gpu_promol_grid_dev(void *hpromol, const int n[3], double *out_dev, int iz0, int iz1, void *stream);

@@ -298,3 +298,6 @@ def promolecular_grid(env: Environ, grids: Grid1Set, n, nthreads=0):
     out = np.zeros(int(n[0]) * int(n[1]) * int(n[2]))
     lib().orc_promolecular_grid(env.ptr, grids.arr, _i(n), _d(out), nthreads)
     return out.reshape(n[2], n[1], n[0])
+
+
+from . import cube_text  # noqa: E402,F401  (formatted-output restatement, pure Python)

@@ -231,6 +231,56 @@ def test_nci_fragments(G, O):
     assert np.array_equal(dev.cpu().numpy().reshape(out["rhofrag"].shape), out["rhofrag"])
 
 
+def _format_samples(rng, n):
+    """Doubles that stress the decimal conversion: all magnitudes, subnormals, exact ties, powers of ten, zeros."""
+    v = [np.ldexp(rng.uniform(0.5, 1.0, n // 2), rng.integers(-1074, 1024, n // 2)) * rng.choice([-1.0, 1.0], n // 2)]
+    v.append(rng.normal(0, 1, n // 8) * 10.0 ** rng.integers(-12, 6, n // 8))
+    ties = []
+    for D in (6, 8, 14):       # N + 1/2 at every decimal position that is exactly representable
+        N = rng.integers(10 ** (D - 1), 10 ** D, 200).astype(float)
+        for p in range(-20, 21):
+            x = (N + 0.5) * 10.0 ** p if p >= 0 else (N + 0.5) / 10.0 ** (-p)
+            ties.append(x)
+    v.append(np.concatenate(ties))
+    v.append(10.0 ** rng.integers(-320, 308, 200))
+    v.append(np.array([0.0, -0.0, 5e-324, -5e-324, 2.2250738585072014e-308, 1.7976931348623157e308, 0.5, 1.5, 2.5,
+                       9.9999995, 99999.95, 0.999999999999995, 1e15 + 50.0, np.inf, -np.inf, np.nan]))
+    out = np.concatenate(v)
+    rng.shuffle(out)
+    return out
+
+
+@pytest.mark.parametrize("force_exact", [0, 1])
+def test_cube_text_matches_fortran_formatting(G, O, force_exact):
+    """writegrid_cube / write_cube_body / .dat text: byte-exact against the formatted-output oracle,
+    fast path and the big-integer rounding path, both record orders, ragged sizes."""
+    ct = O.cube_text
+    rng = np.random.default_rng(123)
+    G.set_option("fmt_force_exact", force_exact)
+    try:
+        for (shape, order) in (((5, 7, 13), 0), ((3, 5, 6), 0), ((6, 3, 11), 1), ((2, 2, 400), 1)):
+            nv = int(np.prod(shape))
+            g = _format_samples(rng, 4096)[:nv].reshape(shape)
+            for fmt in (0, 1, 2):
+                got = G.cube_text(g, fmt, order)
+                ref = ct.cube_body(g, fmt, order)
+                assert len(got) == len(ref)
+                if got != ref:
+                    i = next(k for k in range(len(ref)) if got[k] != ref[k])
+                    raise AssertionError(f"fmt {fmt} order {order}: first difference at byte {i}: "
+                                         f"{got[max(0, i - 30):i + 30]!r} vs {ref[max(0, i - 30):i + 30]!r}")
+        vals = _format_samples(rng, 8192)
+        pairs = vals[:2 * 1000].reshape(-1, 2)
+        assert G.dat_text(pairs) == ct.dat_text(pairs)
+        assert G.dat_text(pairs[:7]) == ct.dat_text(pairs[:7])
+        # every sample once through each format, as one long record
+        g1 = vals.reshape(1, 1, -1)
+        for fmt in (0, 1, 2):
+            assert G.cube_text(g1, fmt, 1) == ct.cube_body(g1, fmt, 1)
+    finally:
+        G.set_option("fmt_force_exact", 0)
+
+
 def test_promolecular_quartz_cube(G, O):
     """Promolecular density of alpha-quartz (periodic, images) with gradient and Hessian on a ragged whole-cell grid."""
     from critic2_b200 import drivers

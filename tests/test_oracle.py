@@ -251,6 +251,32 @@ def test_nci_fragment_density_and_inter_test():
     assert np.all(sums == 0.0)      # no VOID: the void sums stay zero
 
 
+def test_formatted_fields_follow_the_fortran_edit_descriptors():
+    """Hand-checked fields of the three cube formats and the .dat format (Fortran 2008 10.7.2.3.3)."""
+    ct = oracle.cube_text
+    assert ct.field(1.0, 0) == "   0.10000000000000E+01"            # 1x + e22.14
+    assert ct.field(-1234.5678, 0) == "  -0.12345678000000E+04"
+    assert ct.field(1e-100, 0) == "   0.10000000000000E-99"
+    assert ct.field(1e-101, 0) == "   0.10000000000000-100"         # three-digit exponent drops the E
+    assert ct.field(0.0, 0) == "   0.00000000000000E+00"
+    assert ct.field(0.125, 1) == "  1.25000E-01"                    # 1p: one digit before the point
+    assert ct.field(-2.5e-7, 1) == " -2.50000E-07"
+    assert ct.field(1.5e-120, 1) == "  1.50000-120"
+    assert ct.field(123456.5, 2) == "  1.23456E+005"                # exact tie: round half to even
+    assert ct.field(123457.5, 2) == "  1.23458E+005"
+    assert ct.field(-3.0e-5, 2) == " -3.00000E-005"
+    assert ct.fortran_e(0.015625, 15, 7, 1, 2) == "  1.5625000E-02"
+    assert ct.field(float("inf"), 1) == "     Infinity" and ct.field(float("nan"), 2) == "           NaN"
+    # record structure: 6 fields per line, a new line after the last field of every record
+    rec = ct.record(np.arange(8.0), 1)
+    assert rec.count("\n") == 2 and rec.split("\n")[1] == "  6.00000E+00  7.00000E+00"
+    g = np.arange(2 * 3 * 7, dtype=float).reshape(2, 3, 7)         # [iz][iy][ix]
+    body = ct.cube_body(g, 1, 0).decode().split("\n")
+    assert body[0].split() == ["0.00000E+00", "2.10000E+01"]        # record (ix=0, iy=0): iz = 0, 1
+    assert len(body) - 1 == 7 * 3
+    assert ct.dat_text([[0.0123456789, 1.5]]) == b"  1.2345679E-02  1.5000000E+00\n"
+
+
 def test_cube_loop_matches_point_calls_and_layout():
     f = cases.golden_wfn("h2o-wfx")
     st = cases.mol_structure(f)
