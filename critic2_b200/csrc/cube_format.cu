@@ -85,7 +85,7 @@ __device__ static void big_shl(Big &b, int s) {
   while (b.n > 0 && b.w[b.n - 1] == 0) b.n--;
 }
 // sign of m*2^q*10^p - (2N+1)/2
-__device__ static int exact_cmp_half(unsigned long long m, int q, int p, unsigned long long N) {
+__device__ __noinline__ static int exact_cmp_half(unsigned long long m, int q, int p, unsigned long long N) {
   Big X, Y;
   int sx, sy;
   big_set(X, m);
@@ -108,7 +108,7 @@ __device__ __forceinline__ unsigned long long pow10_u64(int k) {
 }
 
 // x finite, non-zero, positive magnitude given by its bits: N (D digits) and e10 with |x| ~ N * 10^(e10 - D + 1)
-__device__ static void to_decimal(unsigned long long bits, int D, int force_exact, unsigned long long &N, int &e10) {
+__device__ __forceinline__ static void to_decimal(unsigned long long bits, int D, int force_exact, unsigned long long &N, int &e10) {
   const int ex = (int)((bits >> 52) & 0x7ff);
   const unsigned long long frac = bits & 0x000fffffffffffffull;
   const unsigned long long m = ex ? (frac | 0x0010000000000000ull) : frac;
@@ -167,47 +167,58 @@ __device__ static void to_decimal(unsigned long long bits, int D, int force_exac
   }
 }
 
-// Writes the field (fs.lead + fs.w characters) of value x at dst.
-__device__ static void format_field(double x, const FmtSpec &fs, int force_exact, char *dst) {
-  const int W = fs.w + fs.lead;
-  char buf[24];
-  for (int i = 0; i < W; i++) buf[i] = ' ';
+// Writes the field (lead + w characters) of value x at dst.  The layout of a finite value is static per format (the
+// content always fills the same columns), so every character goes straight to its place with an immediate offset: no
+// local buffer, no dynamic indexing.
+template <int FMT>
+__device__ __forceinline__ void format_field(double x, int force_exact, char *dst) {
+  constexpr FmtSpec fs = FMT == 0 ? FmtSpec{14, 0, 22, 1, 2, 6}
+                         : FMT == 1 ? FmtSpec{6, 1, 12, 1, 2, 6}
+                         : FMT == 2 ? FmtSpec{6, 1, 13, 1, 3, 6} : FmtSpec{8, 1, 15, 0, 2, 2};
+  constexpr int W = fs.w + fs.lead;
+  constexpr int NEXP = fs.expdig == 3 ? 5 : 4;                 // E+eee | E+ee / +eee
+  constexpr int NFRAC = fs.style == 0 ? fs.D : fs.D - 1;       // digits after the point
+  constexpr int P_EXP = W - NEXP, P_FRAC = P_EXP - NFRAC, P_DOT = P_FRAC - 1, P_LEAD = P_DOT - 1, P_SIGN = P_LEAD - 1;
   const unsigned long long bits = (unsigned long long)__double_as_longlong(x);
   const bool neg = (bits >> 63) != 0;
   const unsigned long long mag = bits & 0x7fffffffffffffffull;
-  int pos = W;   // fill from the right
-  if (mag >= 0x7ff0000000000000ull) {
-    if (mag > 0x7ff0000000000000ull) { buf[--pos] = 'N'; buf[--pos] = 'a'; buf[--pos] = 'N'; }
+  if (mag >= 0x7ff0000000000000ull) {                          // NaN / Infinity, right-justified
+    for (int i = 0; i < W; i++) dst[i] = ' ';
+    if (mag > 0x7ff0000000000000ull) { dst[W - 3] = 'N'; dst[W - 2] = 'a'; dst[W - 1] = 'N'; }
     else {
-      const char *s = "Infinity";
-      for (int i = 7; i >= 0; i--) buf[--pos] = s[i];
-      if (neg) buf[--pos] = '-';
+      const char s[9] = "Infinity";
+      for (int i = 0; i < 8; i++) dst[W - 8 + i] = s[i];
+      if (neg) dst[W - 9] = '-';
     }
-  } else {
-    unsigned long long N = 0;
-    int e10 = 0;
-    if (mag != 0) to_decimal(mag, fs.D, force_exact, N, e10);
-    int E = mag == 0 ? 0 : (fs.style == 0 ? e10 + 1 : e10);
-    int ae = E < 0 ? -E : E;
-    if (fs.expdig == 3 || ae > 99) { buf[--pos] = '0' + ae % 10; ae /= 10; buf[--pos] = '0' + ae % 10; ae /= 10; buf[--pos] = '0' + ae % 10; }
-    else { buf[--pos] = '0' + ae % 10; ae /= 10; buf[--pos] = '0' + ae % 10; }
-    buf[--pos] = E < 0 ? '-' : '+';
-    const int absE = E < 0 ? -E : E;
-    if (fs.expdig == 3 || absE <= 99) buf[--pos] = 'E';
-    // digits, least significant first
-    const int nfrac = fs.style == 0 ? fs.D : fs.D - 1;
-    uint32_t lo7 = (uint32_t)(N % 10000000ull), hi = (uint32_t)(N / 10000000ull);   // N < 10^14
-    for (int i = 0; i < nfrac; i++) {
-      uint32_t &src = i < 7 ? lo7 : hi;
-      buf[--pos] = '0' + (char)(src % 10u);
-      src /= 10u;
-    }
-    buf[--pos] = '.';
-    if (fs.style == 0) buf[--pos] = '0';
-    else { uint32_t &src = nfrac < 7 ? lo7 : hi; buf[--pos] = '0' + (char)(src % 10u); }
-    if (neg) buf[--pos] = '-';
+    return;
   }
-  for (int i = 0; i < W; i++) dst[i] = buf[i];
+  unsigned long long N = 0;
+  int e10 = 0;
+  if (mag != 0) to_decimal(mag, fs.D, force_exact, N, e10);
+  const int E = mag == 0 ? 0 : (fs.style == 0 ? e10 + 1 : e10);
+  const unsigned ae = (unsigned)(E < 0 ? -E : E);
+#pragma unroll
+  for (int i = 0; i < P_SIGN; i++) dst[i] = ' ';
+  dst[P_SIGN] = neg ? '-' : ' ';
+  // digits: N < 10^14 -> two 7-digit halves, least significant first
+  uint32_t lo7 = (uint32_t)(N % 10000000ull), hi7 = (uint32_t)(N / 10000000ull);
+#pragma unroll
+  for (int i = 0; i < NFRAC; i++) {
+    if (i < 7) { dst[P_EXP - 1 - i] = '0' + (char)(lo7 % 10u); lo7 /= 10u; }
+    else { dst[P_EXP - 1 - i] = '0' + (char)(hi7 % 10u); hi7 /= 10u; }
+  }
+  dst[P_DOT] = '.';
+  dst[P_LEAD] = fs.style == 0 ? '0' : (char)('0' + (NFRAC < 7 ? lo7 : hi7) % 10u);
+  const char es = E < 0 ? '-' : '+';
+  if (fs.expdig == 3) {
+    dst[P_EXP] = 'E'; dst[P_EXP + 1] = es;
+    dst[P_EXP + 2] = '0' + (char)(ae / 100u); dst[P_EXP + 3] = '0' + (char)((ae / 10u) % 10u); dst[P_EXP + 4] = '0' + (char)(ae % 10u);
+  } else if (ae <= 99u) {
+    dst[P_EXP] = 'E'; dst[P_EXP + 1] = es; dst[P_EXP + 2] = '0' + (char)(ae / 10u); dst[P_EXP + 3] = '0' + (char)(ae % 10u);
+  } else {
+    dst[P_EXP] = es; dst[P_EXP + 1] = '0' + (char)(ae / 100u); dst[P_EXP + 2] = '0' + (char)((ae / 10u) % 10u);
+    dst[P_EXP + 3] = '0' + (char)(ae % 10u);
+  }
 }
 
 // ---- kernel: groups of 4 records, segments of SEG values ----------------------------------------------------------
@@ -225,9 +236,10 @@ struct FmtArgs {
   long rec_bytes;
 };
 
-__global__ void __launch_bounds__(FMT_NT) format_records_kernel(const FmtArgs a) {
+template <int FMT>
+__global__ void __launch_bounds__(FMT_NT, 3) format_records_kernel(const FmtArgs a) {
   __shared__ __align__(16) char s_buf[FMT_ROWS][FMT_ROWBUF];
-  const FmtSpec fs = fmt_spec(a.fmt);
+  const FmtSpec fs = fmt_spec(FMT);
   const int W = fs.w + fs.lead, L = fs.per_line;
   const int tid = threadIdx.x, dx = tid & (FMT_ROWS - 1), kk = tid >> 2;
   const long ngroup = a.order == 0 ? (long)((a.n1 + FMT_ROWS - 1) / FMT_ROWS) * a.n2 : (a.nrec + FMT_ROWS - 1) / FMT_ROWS;
@@ -258,7 +270,7 @@ __global__ void __launch_bounds__(FMT_NT) format_records_kernel(const FmtArgs a)
         for (int k = kk; k < nk; k += FMT_NT / FMT_ROWS) {
           const double x = a.g[gbase + (size_t)(k0 + k) * gstride];
           char *dst = row + k * W + k / L;
-          format_field(x, fs, a.force_exact, dst);
+          format_field<FMT>(x, a.force_exact, dst);
           if ((k + 1) % L == 0 || k0 + k == a.nval - 1) dst[W] = '\n';
         }
       }
@@ -317,7 +329,12 @@ cudaError_t format_records_launch(const double *g_dev, char *text_dev, long nrec
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
   const int grid = (int)std::min<long>(ngroup, (long)nsm * 6);
-  format_records_kernel<<<grid, FMT_NT, 0, st>>>(a);
+  switch (fmt) {
+    case 0: format_records_kernel<0><<<grid, FMT_NT, 0, st>>>(a); break;
+    case 1: format_records_kernel<1><<<grid, FMT_NT, 0, st>>>(a); break;
+    case 2: format_records_kernel<2><<<grid, FMT_NT, 0, st>>>(a); break;
+    default: format_records_kernel<3><<<grid, FMT_NT, 0, st>>>(a); break;
+  }
   g_launches++;
   return cudaGetLastError();
 }

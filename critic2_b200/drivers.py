@@ -136,3 +136,67 @@ def nciplot(field: "gpu._Field", st: Structure, nstep=None, opts: NciOptions | N
                                       omega=st.omega, rhofrag=rhofrag, rhoparam=opts.rhoparam, rhoparam2=opts.rhoparam2)
     return dict(crho=crho, cgrad=cgrad, cgrad_masked=cg.reshape(cgrad.shape), rhoat=rhoat, rhofrag=rhofrag, sums=sums,
                 dat=dat, ndat=ndat, grid=(x0, xmat, ns))
+
+
+# ---- writers: crystal%writegrid_cube (crystalmod@proc.f90:4965-5041) and the NCIPLOT cubes (nci@proc.f90:769-883) ------
+def _fe(x: float, w: int, d: int) -> str:
+    """Fortran Ew.d (header lines only; the bodies are formatted on the device)."""
+    if x == 0.0:
+        digits, e10 = "0" * d, -1
+    else:
+        mant, ex = ("%.*e" % (d - 1, abs(x))).split("e")
+        digits, e10 = mant.replace(".", ""), int(ex)
+    ex = e10 + 1
+    es = ("E%+03d" % ex) if abs(ex) <= 99 else ("%+04d" % ex)
+    return (("-" if math.copysign(1.0, x) < 0 else "") + "0." + digits + es).rjust(w)
+
+
+def cube_header(st: Structure, n, x0=None, xd=None, precise: bool = True) -> bytes:
+    """Header of writegrid_cube (:5014-5031): two title lines, natoms + origin, three (n, step vector) lines, atoms."""
+    n = [int(v) for v in n]
+    if xd is None:
+        xd = st.m_x2c / np.asarray(n, float)[None, :]
+    x0 = st.molx0 if x0 is None else np.asarray(x0, float)
+    out = ["critic2-cube", "critic2-cube"]
+    if precise:
+        out.append("%5d " % st.ncell + "".join(_fe(float(v), 22, 14) + " " for v in x0))
+        for i in range(3):
+            out.append("%5d " % n[i] + "".join(_fe(float(v), 22, 14) + " " for v in xd[:, i]))
+        for z, r in zip(st.z, st.r):
+            out.append("%4d%5.1f" % (int(z), 0.0) + "".join(_fe(float(v), 22, 14) + " " for v in r + st.molx0))
+    else:
+        out.append("%5d" % st.ncell + "".join("%12.6f" % v for v in x0))
+        for i in range(3):
+            out.append("%5d" % n[i] + "".join("%12.6f" % v for v in xd[:, i]))
+        for z, r in zip(st.z, st.r):
+            out.append("%4d%5.1f" % (int(z), 0.0) + "".join("%11.6f" % v for v in r + st.molx0))
+    return ("\n".join(out) + "\n").encode()
+
+
+def writegrid_cube(path: str, st: Structure, g, x0=None, xd=None, precise: bool = True) -> int:
+    """Write the cube file of a rhoplot_cube property array g[iz][iy][ix] (lf(ix,iy,iz)).  The body -- one record per
+    (ix, iy), iz fastest, 6 values per line (:5026-5036) -- is formatted by the CUDA module; returns the bytes written."""
+    g = np.ascontiguousarray(g, float)
+    n = g.shape[::-1]
+    body = gpu.cube_text(g, gpu.FMT_PRECISE if precise else gpu.FMT_CUBE, order=0)
+    head = cube_header(st, n, x0, xd, precise)
+    with open(path, "wb") as fh:
+        fh.write(head)
+        fh.write(body)
+    return len(head) + len(body)
+
+
+def write_nci_cube_body(fh, c) -> int:
+    """write_cube_body (nci@proc.f90:867-883): c[i][j][k] = crho/cgrad(k,j,i), '(6(1x,1p,e13.5e3))'; the header written
+    by write_cube_header stays with the caller."""
+    body = gpu.cube_text(np.ascontiguousarray(c, float), gpu.FMT_NCI, order=1)
+    fh.write(body)
+    return len(body)
+
+
+def write_nci_dat(path: str, dat) -> int:
+    """The .dat file of NCIPLOT: one '(1p,E15.7,E15.7)' line per (rho, s) pair (nci@proc.f90:593-595)."""
+    text = gpu.dat_text(dat)
+    with open(path, "wb") as fh:
+        fh.write(text)
+    return len(text)

@@ -116,6 +116,27 @@ module gpu_interface
        integer(c_long) :: ndat
        integer(c_int) :: ierr
      end function c2gpu_nci_cutoffs_frag
+     function c2gpu_cube_text_size(n,fmt) bind(c,name="c2gpu_cube_text_size") result(nbytes)
+       import :: c_int, c_long
+       integer(c_int) :: n(3)
+       integer(c_int), value :: fmt
+       integer(c_long) :: nbytes
+     end function c2gpu_cube_text_size
+     function c2gpu_cube_text(g,n,fmt,order,text) bind(c,name="c2gpu_cube_text") result(ierr)
+       import :: c_int, c_double, c_char
+       real(c_double) :: g(*)
+       integer(c_int) :: n(3)
+       integer(c_int), value :: fmt, order
+       character(kind=c_char) :: text(*)
+       integer(c_int) :: ierr
+     end function c2gpu_cube_text
+     function c2gpu_dat_text(npairs,dat,text) bind(c,name="c2gpu_dat_text") result(ierr)
+       import :: c_int, c_long, c_double, c_char
+       integer(c_long), value :: npairs
+       real(c_double) :: dat(2,*)
+       character(kind=c_char) :: text(*)
+       integer(c_int) :: ierr
+     end function c2gpu_dat_text
      function c2gpu_promol_grid(h,n,out) bind(c,name="c2gpu_promol_grid") result(ierr)
        import :: c_int, c_double, c_ptr
        type(c_ptr), value :: h
@@ -424,6 +445,34 @@ contains
     sumq = sums(1); sumqp = sums(2); sumv = sums(3)
     ok = (ierr == 0)
   end subroutine gpu_nci_cutoffs_frag
+
+  !> Body of a cube file written through a stream-access unit: replaces the formatted loops of writegrid_cube
+  !> (crystalmod@proc.f90:5026-5036; fmt 0 = precisecube, 1 = default, order 0: g(ix,iy,iz)) and write_cube_body
+  !> (nci@proc.f90:867-883; fmt 2, order 1: c(k,j,i)).  The header is written by the caller as today; the unit is then
+  !> re-opened with access='stream', position='append' and the text block written in one statement.
+  subroutine gpu_write_cube_body(file,g,n,fmt,order,ok)
+    character*(*), intent(in) :: file
+    real(c_double), intent(in) :: g(*)
+    integer, intent(in) :: n(3), fmt, order
+    logical, intent(out) :: ok
+    character(kind=c_char), allocatable :: text(:)
+    integer(c_int) :: ierr, nn(3)
+    integer(c_long) :: nbytes
+    integer :: lu
+    ok = .false.
+    if (.not.gpu_enabled) return
+    nn = int(n,c_int)
+    nbytes = c2gpu_cube_text_size(nn,int(fmt,c_int))
+    if (nbytes <= 0) return
+    allocate(text(nbytes))
+    ierr = c2gpu_cube_text(g,nn,int(fmt,c_int),int(order,c_int),text)
+    call gpu_check("write_cube_body",ierr)
+    if (ierr /= 0) return
+    open(newunit=lu,file=file,access='stream',form='unformatted',position='append',status='old')
+    write(lu) text
+    close(lu)
+    ok = .true.
+  end subroutine gpu_write_cube_body
 
   !> Replacement of the promolecular_grid loop (crystalmod@proc.f90:5143-5158): f(n1,n2,n3), nder = 0.
   subroutine gpu_promolecular_grid(h,n,f,ok)

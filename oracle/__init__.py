@@ -13,7 +13,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = os.path.join(_HERE, "_build", "liboracle.so")
-_SRC = ["oracle_env.c", "oracle_wfn.c", "oracle_promol.c", "oracle_field.c", "oracle.h", "oracle_util.h"]
+_SRC = ["oracle_env.c", "oracle_wfn.c", "oracle_promol.c", "oracle_field.c", "oracle_text.c", "oracle.h", "oracle_util.h"]
 
 
 def build(force: bool = False) -> str:
@@ -67,6 +67,9 @@ def lib():
         L.orc_nci_cutoffs_frag.restype = C.c_long
         L.orc_nci_cutoffs_frag.argtypes = [ip, dp, dp, dp, C.c_int, dp, C.c_double, C.c_double, C.c_double, C.c_double,
                                            C.c_double, dp, C.c_int, C.c_double, C.c_double, dp, dp, C.c_long]
+        L.orc_text_record_bytes.restype = C.c_long
+        L.orc_text_record_bytes.argtypes = [C.c_int, C.c_int]
+        L.orc_cube_text.argtypes = [dp, ip, C.c_int, C.c_int, C.c_char_p, C.c_int]
         L.orc_promolecular_grid.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), ip, dp, C.c_int]
         L.orc_grd_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
         L.orc_nact_points.argtypes = [C.c_void_p, C.c_void_p, C.c_long, dp, C.POINTER(C.c_long), C.c_int]
@@ -301,3 +304,13 @@ def promolecular_grid(env: Environ, grids: Grid1Set, n, nthreads=0):
 
 
 from . import cube_text  # noqa: E402,F401  (formatted-output restatement, pure Python)
+
+
+def cube_text_c(g, fmt: int, order: int, nthreads: int = 0) -> bytes:
+    """C version of cube_text.cube_body (same bytes) for large arrays and the timed CPU baseline."""
+    g = _f64(g)
+    n = _i32(g.shape[::-1] if order == 0 else g.shape)
+    nb = int(n[0]) * int(n[1]) * int(lib().orc_text_record_bytes(int(n[2]), fmt))
+    buf = C.create_string_buffer(nb)
+    lib().orc_cube_text(_d(g), _i(n), fmt, order, buf, nthreads)
+    return buf.raw

@@ -143,6 +143,9 @@ long orc_nci_cutoffs_frag(const int *nstep, double *crho, double *cgrad, const d
                           double *sums, double *dat, long maxdat);
 /* promolecular_grid (src/crystalmod@proc.f90:5118-5158): whole-cell grid at fractional nodes (i-1)/n, nder=0 */
 void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, double *out, int nthreads);
+/* formatted cube bodies (oracle_text.c): writegrid_cube / write_cube_body / .dat text */
+long orc_text_record_bytes(int nval, int fmt);
+void orc_cube_text(const double *g, const int *n, int fmt, int order, char *text, int nthreads);
 /* evaluate grd on an arbitrary list of points: res is npts*ORC_RES_LEN */
 void orc_grd_points(const orc_field *f, long npts, const double *pts, int nder, int periodic, double *res, int nthreads);
 void orc_nact_points(const orc_wfn *f, const orc_environ *env, long npts, const double *pts, long *nact, int nthreads);

@@ -281,6 +281,37 @@ def test_cube_text_matches_fortran_formatting(G, O, force_exact):
         G.set_option("fmt_force_exact", 0)
 
 
+def test_written_cube_file_round_trips(G, O, tmp_path):
+    """CUBE -> writegrid_cube: header as crystalmod@proc.f90:5014-5031, body = the oracle's text, values recovered to the
+    14 printed digits; the NCIPLOT body and .dat writers likewise."""
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("h2o-wfx")
+    st = cases.mol_structure(f)
+    fld = G.WfnField(f, st)
+    res, (o, xd, nn) = drivers.rhoplot_cube(fld, st, (9, 7, 11), props=("f", "lap"))
+    path = tmp_path / "rho.cube"
+    nbytes = drivers.writegrid_cube(str(path), st, res["f"], precise=True)
+    raw = path.read_bytes()
+    assert len(raw) == nbytes
+    lines = raw.decode().split("\n")
+    assert lines[0] == "critic2-cube" and int(lines[2].split()[0]) == st.ncell
+    assert [int(lines[3 + i].split()[0]) for i in range(3)] == [9, 7, 11]
+    head = drivers.cube_header(st, (9, 7, 11))
+    assert raw[len(head):] == O.cube_text.cube_body(res["f"], 0, 0)
+    vals = np.array(" ".join(lines[6 + st.ncell:]).split(), float).reshape(9, 7, 11)   # (ix, iy, iz)
+    np.testing.assert_allclose(vals, res["f"].transpose(2, 1, 0), rtol=5.1e-14, atol=0)
+    # NCIPLOT cube body + .dat
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(6, 5, 7))
+    crho, cgrad, _ = fld.nci(x0, xmat, ns)
+    with open(tmp_path / "dens.cube", "wb") as fh:
+        drivers.write_nci_cube_body(fh, crho)
+    assert (tmp_path / "dens.cube").read_bytes() == O.cube_text.cube_body(crho, 2, 1)
+    cg = cgrad.reshape(-1).copy()
+    sums, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg)
+    drivers.write_nci_dat(str(tmp_path / "nci.dat"), dat)
+    assert (tmp_path / "nci.dat").read_bytes() == O.cube_text.dat_text(dat)
+
+
 def test_promolecular_quartz_cube(G, O):
     """Promolecular density of alpha-quartz (periodic, images) with gradient and Hessian on a ragged whole-cell grid."""
     from critic2_b200 import drivers

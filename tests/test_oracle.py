@@ -275,6 +275,14 @@ def test_formatted_fields_follow_the_fortran_edit_descriptors():
     assert body[0].split() == ["0.00000E+00", "2.10000E+01"]        # record (ix=0, iy=0): iz = 0, 1
     assert len(body) - 1 == 7 * 3
     assert ct.dat_text([[0.0123456789, 1.5]]) == b"  1.2345679E-02  1.5000000E+00\n"
+    # the C version (large arrays, CPU baseline) writes the same bytes
+    rng = np.random.default_rng(11)
+    vals = np.concatenate([np.ldexp(rng.uniform(0.5, 1, 600), rng.integers(-1074, 1024, 600)) * rng.choice([-1, 1], 600),
+                           [0.0, -0.0, np.inf, -np.inf, np.nan, 1e-101, 123456.5, 123457.5, 5e-324, 1e6, 1e14, 1e8]])
+    for shape, order in (((4, 9, 17), 0), ((6, 6, 17), 1)):
+        arr = vals.reshape(shape)
+        for fmt in (0, 1, 2):
+            assert oracle.cube_text_c(arr, fmt, order) == ct.cube_body(arr, fmt, order)
 
 
 def test_cube_loop_matches_point_calls_and_layout():

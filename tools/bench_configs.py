@@ -19,7 +19,7 @@ from critic2_b200 import drivers, gpu, structure, synth  # noqa: E402
 import cases  # noqa: E402
 
 FP64_DMMA_TFLOPS, FP64_DFMA_TFLOPS = 37.1, 34.0    # profiles/r1_fp64_peak_microbench.log
-HBM_GBS = 6540.0                                   # B200_PROFILING.md fallback copy bandwidth
+HBM_GBS = 6552.0                                   # MEASURED_PEAKS.json hbm_gbs (copy bandwidth)
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--cfgs", default="1,2,3,5")
