@@ -200,3 +200,44 @@ def write_nci_dat(path: str, dat) -> int:
     with open(path, "wb") as fh:
         fh.write(text)
     return len(text)
+
+
+# ---- point-list callers of field%grd: LINE, PLANE, mesh fill -----------------------------------
+_RES_OF_NTI = {0: 0, 1: 1, 2: 2, 3: 3, 4: 13, 5: 4, 6: 7, 7: 10, 8: 8, 9: 11, 10: 12, 11: 14}   # res column of nti
+
+
+def _nder_of(nti: int) -> int:
+    return 0 if nti == 0 else (1 if nti <= 4 else 2)          # rhoplot@proc.f90:279-285, 891-897
+
+
+def rhoplot_line(field: "gpu._Field", st: Structure, x0, x1, npts: int, prop: str = "f"):
+    """LINE x0 x1 npts [prop] (rhoplot@proc.f90:276-325): x0, x1 Cartesian (cell frame, bohr).  Returns
+    (xp (npts,3), rhoout, lapout): rhoout = f, lapout = the selected property, like the reference's two columns."""
+    nti = gpu.PROPS.index(prop)
+    x0, x1 = np.asarray(x0, float), np.asarray(x1, float)
+    t = np.arange(npts, dtype=float) / float(npts - 1)
+    xp = x0[None, :] + (x1 - x0)[None, :] * t[:, None]          # :278
+    res = field.points(xp, nder=_nder_of(nti), periodic=not st.ismolecule)
+    return xp, res[:, 0].copy(), res[:, _RES_OF_NTI[nti]].copy()
+
+
+def rhoplot_plane(field: "gpu._Field", st: Structure, x0, x1, x2, nx: int, ny: int, prop: str = "f"):
+    """PLANE x0 x1 x2 nx ny [prop] (rhoplot@proc.f90:880-940, without SCALE/EXTENDXY): ff(nx,ny) with
+    xp = x0 + (ix-1) uu + (iy-1) vv, uu = (x1-x0)/(nx-1), vv = (x2-x0)/(ny-1).  Returns ff (nx, ny)."""
+    nti = gpu.PROPS.index(prop)
+    x0, x1, x2 = (np.asarray(v, float) for v in (x0, x1, x2))
+    uu, vv = (x1 - x0) / float(nx - 1), (x2 - x0) / float(ny - 1)
+    ix, iy = np.meshgrid(np.arange(nx, dtype=float), np.arange(ny, dtype=float), indexing="ij")
+    xp = x0[None, None, :] + ix[..., None] * uu + iy[..., None] * vv
+    res = field.points(xp.reshape(-1, 3), nder=_nder_of(nti), periodic=not st.ismolecule)
+    return res[:, _RES_OF_NTI[nti]].reshape(nx, ny)
+
+
+def mesh_fill(field: "gpu._Field", pts, props=("rho",), periodic: bool = True):
+    """mesh%fill (meshmod@proc.f90:446-470) for the properties the path provides: 'volume' (1), 'rho' (res%f),
+    'gradrho' (res%gfmod).  pts (n,3) Cartesian mesh nodes; returns f (n, len(props))."""
+    nder = max([-1] + [{"volume": -1, "rho": 0, "gradrho": 1}[p] for p in props])
+    pts = np.asarray(pts, float).reshape(-1, 3)
+    res = field.points(pts, nder=nder, periodic=periodic) if nder >= 0 else None
+    cols = {"volume": lambda: np.ones(pts.shape[0]), "rho": lambda: res[:, 0], "gradrho": lambda: res[:, 13]}
+    return np.stack([cols[p]() for p in props], axis=1)

@@ -312,6 +312,31 @@ def test_written_cube_file_round_trips(G, O, tmp_path):
     assert (tmp_path / "nci.dat").read_bytes() == O.cube_text.dat_text(dat)
 
 
+def test_line_plane_and_mesh_drivers(G, O):
+    """The point-list callers of grd: LINE, PLANE, mesh fill against the oracle's grd."""
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("hooh-atz")
+    st = cases.mol_structure(f)
+    of = _ofield(O, f, st)
+    fld = G.WfnField(f, st)
+    a, b = st.r[0] + np.array([0.3, -0.2, 0.1]), st.r[-1] + np.array([1.5, 1.0, -0.7])
+    xp, rho, lap = drivers.rhoplot_line(fld, st, a, b, 41, "lap")
+    ref = of.grd_points(xp, nder=2, periodic=False)
+    check_rho(rho, ref[:, 0], "line rho")
+    hn = np.sqrt((ref[:, 4:13] ** 2).sum(1))
+    assert (np.abs(lap - ref[:, 14]) / np.maximum(hn, 1e-4 * np.abs(ref[:, 0]))).max() <= cases.TOL_DER
+    c = st.r.mean(0)
+    ff = drivers.rhoplot_plane(fld, st, c + [-3, -3, 0.2], c + [3, -3, 0.2], c + [-3, 3, 0.2], 13, 11, "gmod")
+    ix, iy = np.meshgrid(np.arange(13.0), np.arange(11.0), indexing="ij")
+    pts = (c + [-3, -3, 0.2])[None, None, :] + ix[..., None] * np.array([0.5, 0, 0]) + iy[..., None] * np.array([0, 0.6, 0])
+    refp = of.grd_points(pts.reshape(-1, 3), nder=1, periodic=False)
+    check_vec(ff.reshape(-1, 1), refp[:, 13:14], "plane gmod", rho=refp[:, 0])
+    m = drivers.mesh_fill(fld, pts.reshape(-1, 3)[:50], ("volume", "rho", "gradrho"), periodic=False)
+    assert np.all(m[:, 0] == 1.0)
+    check_rho(m[:, 1], refp[:50, 0], "mesh rho")
+    check_vec(m[:, 2:3], refp[:50, 13:14], "mesh gradrho", rho=refp[:50, 0])
+
+
 def test_promolecular_quartz_cube(G, O):
     """Promolecular density of alpha-quartz (periodic, images) with gradient and Hessian on a ragged whole-cell grid."""
     from critic2_b200 import drivers
