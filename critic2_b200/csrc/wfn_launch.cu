@@ -14,6 +14,11 @@ long g_launches = 0;
   X(3, "L", 2, 7, 14, 28, 1)  \
   X(4, "L1", 1, 7, 14, 28, 2) \
   X(5, "L16", 2, 8, 14, 32, 1)
+// id after the warp-specialised kernel (id 6): 9..24 MOs with the 24 columns spread over three warp columns, so a thread
+// holds 20 accumulators instead of 60 and two CTAs (24 warps) are resident per SM instead of one (8 warps); measured on
+// benzene NCIPLOT 200^3: 20.9 ms against 22.0 ms for S3 (P = 64 and P = 16 variants of the same idea were slower)
+#define C2_WFN_CONFIGS2(X) \
+  X(7, "S3w", 4, 3, 3, 12, 2)
 
 static void tile_shape(int P, int &ta, int &tb, int &tc) {
   switch (P) {
@@ -47,6 +52,19 @@ static std::vector<WfnCfgInfo> build_infos() {
     i.smem[0] = WsCfg<1>::SMEM; i.smem[1] = WsCfg<4>::SMEM; i.smem[2] = WsCfg<10>::SMEM;
     v.push_back(i);
   }
+#define X(ID, NAME, WM, WN, NF, KC, CTAS)                                                            \
+  {                                                                                                  \
+    WfnCfgInfo i;                                                                                    \
+    i.name = NAME; i.wm = WM; i.wn = WN; i.ni = NF; i.kc = KC; i.ctas = CTAS;                        \
+    i.P = 8 * WM; i.NB = 8 * NF; i.NT = 32 * WM * WN;                                           \
+    tile_shape(i.P, i.ta, i.tb, i.tc);                                                               \
+    i.smem[0] = TileCfg<1, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[1] = TileCfg<4, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[2] = TileCfg<10, WM, WN, NF, KC, CTAS>::SMEM;                                             \
+    v.push_back(i);                                                                                  \
+  }
+  C2_WFN_CONFIGS2(X)
+#undef X
   return v;
 }
 
@@ -61,7 +79,7 @@ int wfn_choose_config(int nmo, int force) {
   if (force >= 0 && force < wfn_num_configs()) return force;
   int nfrag = (nmo + 7) / 8;
   if (nfrag <= 1) return 0;
-  if (nfrag <= 3) return 1;
+  if (nfrag <= 3) return 7;
   int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
   return (padM < padL) ? 2 : 6;
 }
@@ -109,6 +127,7 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
     return launch_one<TileCfg<10, WM, WN, NF, KC, CTAS>>(p, grid, st);             \
   }
   C2_WFN_CONFIGS(X)
+  C2_WFN_CONFIGS2(X)
 #undef X
   return cudaErrorInvalidValue;
 }
