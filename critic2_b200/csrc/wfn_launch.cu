@@ -81,7 +81,11 @@ int wfn_choose_config(int nmo, int force) {
   if (nfrag <= 1) return 0;
   if (nfrag <= 3) return 7;
   int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
-  return (padM < padL) ? 2 : 6;
+  if (padM < padL) return 2;
+  // The warp-specialised kernel amortises its chi-tile cache over the MO blocks: measured on a 60-atom molecule it only
+  // ties the block-synchronous L at 2 blocks (nmo = 200: 200.6 vs 196.9 ms) and loses at 1 block; at 7 blocks (cfg 4) it
+  // wins 88 % to 62 %.  A 64-column variant of it (WsCfg<ND, 8>) measured no better than M/L for 48-200 MOs.
+  return nmo > 2 * 112 ? 6 : 3;
 }
 
 template <class C>

@@ -15,18 +15,22 @@
 
 namespace c2 {
 
-template <int ND_>
+// NFRAG_ = 8-column fragments per MO block: 14 (NB = 112, large MO counts) or 8 (NB = 64, a few dozen to ~200 MOs, where
+// 112-column blocks would pad too much).  Warp columns 0,1 (warpgroup 0) own NF0 fragments each, 2,3 (warpgroup 1) NF1.
+template <int ND_, int NFRAG_ = 14>
 struct WsCfg {
   static constexpr int ND = ND_;
   static constexpr int P = 16, WM = 2;          // points per sub-tile (two 8-point MMA row groups)
-  static constexpr int NFRAG = 14, NB = 112;    // MO columns per block
+  static constexpr int NFRAG = NFRAG_, NB = 8 * NFRAG_;    // MO columns per block
+  static constexpr int NF0 = (NFRAG_ + 3) / 4, NF1 = (NFRAG_ - 2 * NF0) / 2;
+  static_assert(2 * NF0 + 2 * NF1 == NFRAG_ && NF1 >= 1 && NB % 16 == 0, "fragment split");
   static constexpr int NCW = 8, NPW = 4;        // consumer / producer warps
   static constexpr int NT = 32 * (NCW + NPW);
   static constexpr int NCT = 32 * NCW, NPT = 32 * NPW;
   static constexpr int KC = 32, NKQ = KC / 4;   // primitives per stage
   static constexpr int NS = 3;                  // stages
-  static constexpr int NI = 4;                  // most fragments per consumer warp
-  static constexpr int SB = 116;                // B row stride in doubles (= 4 mod 16)
+  static constexpr int NI = NF0;                // most fragments per consumer warp
+  static constexpr int SB = NB + 4;             // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
   static constexpr int TSLOTS = 8;              // tile-info ring (>= NS + 3, see ws_generator)
   static constexpr int NPART = 2 * 4 * P * ND;  // s_part doubles: [2 sub-tile parities][4 warp columns][P][ND]
@@ -464,7 +468,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
   constexpr int ND = C::ND, P = C::P, NS = C::NS, NB = C::NB, SB = C::SB, NCT = C::NCT;
   const int lane = ctid & 31, cw = ctid >> 5;
   const int wm = cw & 1, wn = cw >> 1;                 // row group (8 points) and warp column (0..3)
-  const int f0 = wn < 2 ? wn * 4 : 8 + (wn - 2) * 3;   // first fragment of this warp: 4,4,3,3 fragments
+  const int f0 = wn < 2 ? wn * C::NF0 : 2 * C::NF0 + (wn - 2) * C::NF1;   // first fragment of this warp (4,4,3,3 for NB = 112)
   const int row = lane >> 2;
   const int aoff = row * 4 + ((lane & 3) ^ (((wm * 8 + row) >> 2) & 3));
   const WfnDev &w = p.w;
@@ -651,10 +655,10 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
     else ws_generator<C>(p, S, tid - C::NCT - 32);
   } else if (tid < 128) {
     reg_inc<C::REG_CONS4>();
-    ws_consumer<C, 4>(p, S, tid);
+    ws_consumer<C, C::NF0>(p, S, tid);
   } else {
     reg_inc<C::REG_CONS3>();
-    ws_consumer<C, 3>(p, S, tid);
+    ws_consumer<C, C::NF1>(p, S, tid);
   }
 }
 #endif
