@@ -45,7 +45,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-stride", type=int, default=8, help="sub-lattice stride of the CPU sample")
-    return ap.parse_args()
+    ap.add_argument("--aux", default="", choices=["", "configs", "format"],
+                    help="secondary measurements with their CPU baselines: BASELINE configs 1,2,3,5 (tools/bench_configs.py) "
+                         "or the cube-text formatter (tools/bench_format.py); extra arguments go to the tool")
+    return ap.parse_known_args()
 
 
 def workload(n):
@@ -113,6 +116,64 @@ def cpu_sample(f, st, lo, xd, nn, stride, reps=1):
         res = fld.grd_points(pts, nder=2, periodic=False, nthreads=cores)
     dt = (time.perf_counter() - t0) / reps
     return pts, res, dt, cores
+
+
+class CpuLegs:
+    """CPU baselines of the secondary measurements (--aux): the oracle on all host cores, bounded samples.  bench.py is
+    the only non-test code that runs the oracle; tools/bench_*.py receive this object and never import it."""
+
+    def __init__(self):
+        import oracle
+        oracle.build()
+        self.o = oracle
+        self.cores = os.cpu_count() or 1
+
+    def _res(self, npts, dt, sample):
+        return {"value": npts / dt, "unit": "points/s", "cores": self.cores, "kind": "port", "sample": sample}
+
+    def cube(self, f, st, x0, xd, nn, props):
+        fld = self.o.Field(self.o.Environ(st), wfn=self.o.Wfn(f))
+        t0 = time.perf_counter()
+        fld.cube(x0, xd, nn, props=tuple(props), periodic=False, nthreads=self.cores)
+        return self._res(int(np.prod(nn)), time.perf_counter() - t0, "full grid, one nder=2 evaluation per point")
+
+    def nci(self, f, st, x0, xmat, ns):
+        fld = self.o.Field(self.o.Environ(st), wfn=self.o.Wfn(f))
+        sub = np.array([max(1, int(ns[0]) // 8), int(ns[1]), int(ns[2])], np.int32)     # every 8th x-plane
+        xm = np.array(xmat, float).copy()
+        xm[:, 0] *= float(ns[0]) / float(sub[0])
+        t0 = time.perf_counter()
+        fld.nci(x0, xm, sub, nthreads=self.cores)
+        return self._res(int(np.prod(sub)), time.perf_counter() - t0, f"{sub[0]} of {int(ns[0])} x-planes, NCIPLOT evaluation loop")
+
+    def promol(self, st, tables, x0, xd, nn, nder):
+        fld = self.o.Field(self.o.Environ(st), grids=self.o.Grid1Set(tables))
+        sub = np.array([int(nn[0]), int(nn[1]), max(1, int(nn[2]) // 16)], np.int32)  # every 16th z-plane
+        xs = np.array(xd, float).copy()
+        xs[:, 2] *= float(nn[2]) / float(sub[2])
+        idx = [np.arange(int(n)) for n in sub]
+        I, J, K = np.meshgrid(*idx, indexing="ij")
+        pts = np.asarray(x0, float)[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ xs.T
+        t0 = time.perf_counter()
+        fld.grd_points(pts, nder=nder, periodic=True, nthreads=self.cores)
+        return self._res(len(pts), time.perf_counter() - t0, f"{sub[2]} of {int(nn[2])} z-planes, nder={nder}")
+
+    def text(self, sample, fmt):
+        t0 = time.perf_counter()
+        self.o.cube_text_c(sample, fmt, 1, nthreads=self.cores)
+        return {"value": sample.size / (time.perf_counter() - t0), "unit": "values/s", "cores": self.cores, "kind": "port",
+                "sample": f"{sample.shape[0]}^3 values, C oracle (glibc %.*E, OpenMP)"}
+
+
+def run_aux(a, rest):
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    cpu = None if a.no_cpu else CpuLegs()
+    if a.aux == "configs":
+        import bench_configs
+        bench_configs.main(rest, cpu)
+    else:
+        import bench_format
+        bench_format.main(rest, cpu)
 
 
 def run_reference(a):
@@ -283,8 +344,10 @@ def run_ours(a):
 
 
 if __name__ == "__main__":
-    args = parse()
-    if args.impl == "reference":
+    args, rest = parse()
+    if args.aux:
+        run_aux(args, rest)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
