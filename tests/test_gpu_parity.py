@@ -91,6 +91,30 @@ def test_cube_synthetic_all_configs(G, O, cfg, variant):
     print(cfg, variant, _compare_cube(got, ref))
 
 
+@pytest.mark.parametrize("cfg", [3, 6, 7])
+def test_point_lists_through_every_kernel_family(G, O, cfg):
+    """c2gpu_eval_points (ragged list: 1 000 points is not a multiple of any tile) through the block-synchronous, the
+    warp-specialised and the small-MO kernels."""
+    from critic2_b200 import synth
+    f = synth.small_synthetic()
+    st = cases.mol_structure(f)
+    rng = np.random.default_rng(5)
+    lo, hi = st.r.min(0) - 2.5, st.r.max(0) + 2.5
+    pts = rng.uniform(lo, hi, (1000, 3))
+    pts[:3] = st.r[:3]                                   # nuclei: gradient forced to zero (fieldmod :836-838)
+    ref = _ofield(O, f, st).grd_points(pts, nder=2, periodic=False)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    got = fld.points(pts, nder=2, periodic=False)
+    check_rho(got[:, 0], ref[:, 0], "rho")
+    check_vec(got[:, 1:4], ref[:, 1:4], "grad", rho=ref[:, 0])
+    check_vec(got[:, 4:13], ref[:, 4:13], "hess", rho=ref[:, 0])
+    assert np.array_equal(got[:, 15] != 0, ref[:, 15] != 0) and np.all(got[:3, 1:4] == 0.0)
+
+
 @pytest.mark.parametrize("nder", [0, 1])
 def test_lower_nder(G, O, nder):
     f = cases.golden_wfn("benzene-adz")

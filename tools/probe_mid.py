@@ -5,7 +5,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from critic2_b200 import gpu, structure, synth
 gpu.init_devices([0])
 n = 160
-for nmo in (48, 150, 200):
+import os as _os
+for nmo in [int(v) for v in _os.environ.get('PROBE_NMO', '48,150,200').split(',')]:
     f = synth.synthetic_molecule(lattice=(4, 4, 4), ndrop=4, composition=((6, 24), (7, 3), (8, 3), (1, 30)), seed=7, nmo=nmo) \
         if "nmo" in synth.synthetic_molecule.__code__.co_varnames else synth.small_synthetic(nmo=nmo)
     st = structure.molecular_cell(f.xyz, f.z)
@@ -15,7 +16,7 @@ for nmo in (48, 150, 200):
     outs = [torch.zeros(n ** 3, dtype=torch.float64, device="cuda") for _ in props]
     s = torch.cuda.current_stream().cuda_stream
     ref = None
-    for cfg in (2, 3, 6):
+    for cfg in [int(v) for v in _os.environ.get('PROBE_CFG', '2,3,6').split(',')]:
         gpu.set_option("wfn_cfg", cfg)
         fld = gpu.WfnField(f, st)
         nact = fld.count_active(lo, xd, nn)
