@@ -26,11 +26,26 @@ struct GridDesc {
   int nci_order;   // 0: a=i0,b=i1,c=i2   1: a=i2,b=i1,c=i0
   int c0, c1;      // evaluated range of the slowest output axis
   int c_part, c_nparts;  // of the layers of height sc (tc for the promolecular kernel) inside [c0,c1), evaluate those with index = c_part mod c_nparts
+  int part_rows;   // 1: the interleaved unit is a b-row of (super-)tiles of a layer, unit = layer * ntb + ib (finer balance)
   int periodic;
   const double *pts;  // non-null: explicit point list (n[0] points, n[1]=n[2]=1), 3 doubles per point
   int ta, tb, tc;  // sub-tile shape (ta*tb*tc = points per tile)
   int sa, sb, sc;  // super-tile shape (multiples of the sub-tile shape)
 };
+
+// Work item `st` of this part -> (super-)tile indices along a, b and the layer index along c (nta, ntb tiles along a, b).
+__host__ __device__ inline void part_item(const GridDesc &g, int st, int nta, int ntb, int &ia, int &ib, int &ic) {
+  ia = st % nta;
+  const int r = st / nta;
+  if (g.part_rows) { const int u = g.c_part + r * g.c_nparts; ib = u % ntb; ic = u / ntb; }
+  else { ib = r % ntb; ic = g.c_part + (r / ntb) * g.c_nparts; }
+}
+// Number of work items of this part for nlayers layers.
+__host__ __device__ inline long part_items(const GridDesc &g, int nta, int ntb, int nlayers) {
+  const long units = g.part_rows ? (long)nlayers * ntb : nlayers;
+  const long mine = g.c_part < units ? (units - g.c_part + g.c_nparts - 1) / g.c_nparts : 0;
+  return g.part_rows ? mine * nta : mine * nta * ntb;
+}
 
 __host__ __device__ inline int grid_na(const GridDesc &g) { return g.nci_order ? g.n[2] : g.n[0]; }
 __host__ __device__ inline int grid_nb(const GridDesc &g) { return g.n[1]; }

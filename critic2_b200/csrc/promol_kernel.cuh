@@ -113,7 +113,9 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
   const GridDesc &g = p.g;
   const int na = grid_na(g), nb = grid_nb(g);
   const int t = blockIdx.x;
-  const int ta0 = (t % p.nta) * g.ta, tb0 = ((t / p.nta) % p.ntb) * g.tb, tc0 = g.c0 + (g.c_part + (t / (p.nta * p.ntb)) * g.c_nparts) * g.tc;
+  int ia, ib, ic;
+  part_item(g, t, p.nta, p.ntb, ia, ib, ic);
+  const int ta0 = ia * g.ta, tb0 = ib * g.tb, tc0 = g.c0 + ic * g.tc;
   const int a = ta0 + tid % g.ta, b = tb0 + (tid / g.ta) % g.tb, c = tc0 + tid / (g.ta * g.tb);
   const bool valid = a < na && b < nb && c < g.c1;
 

@@ -26,7 +26,8 @@ struct WfnParams {
   CellXf xf;
   OutDesc o;
   int nblk;             // MO blocks (ldc = nblk*NB)
-  int nsa, nsb, nsc;    // super-tile counts along (a,b,c)
+  int nsa, nsb, nsc;    // super-tile counts along (a,b) and layers of this part
+  int nitems;           // work items (super-tiles) of this part
   int *work_counter;    // dynamic super-tile scheduler
   int *scratch;         // per CTA: shell list [shell_cap] then primitive list [prim_cap]
   int shell_cap, prim_cap;
@@ -136,8 +137,10 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
     if (tid == 0) s_int[0] = atomicAdd(p.work_counter, 1);
     __syncthreads();
     const int st = s_int[0];
-    if (st >= p.nsa * p.nsb * p.nsc) break;
-    const int sa0 = (st % p.nsa) * g.sa, sb0 = ((st / p.nsa) % p.nsb) * g.sb, sc0 = g.c0 + (g.c_part + (st / (p.nsa * p.nsb)) * g.c_nparts) * g.sc;
+    if (st >= p.nitems) break;
+    int ia, ib, ic;
+    part_item(g, st, p.nsa, p.nsb, ia, ib, ic);
+    const int sa0 = ia * g.sa, sb0 = ib * g.sb, sc0 = g.c0 + ic * g.sc;
 
     // ---- S1: super-tile bounding box of the (wrapped) evaluation points ---------------------------------------
     {

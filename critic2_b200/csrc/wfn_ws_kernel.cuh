@@ -143,9 +143,10 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
     if (gtid == 0) S.p_int[0] = atomicAdd(p.work_counter, 1);
     named_bar_sync(2, NGT);
     const int st = S.p_int[0];
-    if (st >= p.nsa * p.nsb * p.nsc) break;
-    const int sa0 = (st % p.nsa) * g.sa, sb0 = ((st / p.nsa) % p.nsb) * g.sb;
-    const int sc0 = g.c0 + (g.c_part + (st / (p.nsa * p.nsb)) * g.c_nparts) * g.sc;
+    if (st >= p.nitems) break;
+    int ia, ib, ic;
+    part_item(g, st, p.nsa, p.nsb, ia, ib, ic);
+    const int sa0 = ia * g.sa, sb0 = ib * g.sb, sc0 = g.c0 + ic * g.sc;
     // ---- S1: super-tile box, ordered shell compaction, nucleus candidates ---------------------------------------
     {
       double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};

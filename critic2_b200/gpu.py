@@ -54,6 +54,7 @@ def lib():
                                           C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_eval_grid_dev_part.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint,
                                                C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_eval_grid_dev_part_rows.argtypes = L.c2gpu_eval_grid_dev_part.argtypes
         L.c2gpu_layer_height.argtypes = [C.c_void_p]
         L.c2gpu_nci_grid_dev_part.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_int, C.c_int, C.c_void_p]
@@ -189,14 +190,15 @@ class _Field:
                                          iz0, int(nna[2]) if iz1 is None else iz1, C.c_void_p(stream)))
 
     def cube_dev_part(self, x0, xd, nn, outs, props, part: int, nparts: int, nder: int = 2, periodic: bool = False,
-                      stream: int = 0):
-        """Like cube_dev for the interleaved z layers (layer % nparts == part): the multi-GPU decomposition."""
+                      stream: int = 0, rows: bool = False):
+        """Like cube_dev for the interleaved z layers (layer % nparts == part): the multi-GPU decomposition.
+        rows=True interleaves rows of super-tiles instead of whole layers (finer balance; gather by reduction)."""
         x0a, xda, nna = _grid_args(x0, xd, nn)
         names = [p for p in PROPS if p in props]
         mask = sum(1 << PROPS.index(p) for p in names)
         ptrs = (C.c_void_p * len(outs))(*[C.c_void_p(t.data_ptr()) for t in outs])
-        _check(lib().c2gpu_eval_grid_dev_part(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs,
-                                              part, nparts, C.c_void_p(stream)))
+        fn = lib().c2gpu_eval_grid_dev_part_rows if rows else lib().c2gpu_eval_grid_dev_part
+        _check(fn(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs, part, nparts, C.c_void_p(stream)))
 
     def layer_height(self) -> int:
         return int(lib().c2gpu_layer_height(self.handle))

@@ -89,6 +89,13 @@ int c2gpu_eval_grid_dev(void *h, const double x0[3], const double xd[9], const i
 int c2gpu_eval_grid_dev_part(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
                              unsigned outmask, double *const *out_dev, int part, int nparts, void *stream);
 /* height of those layers for handle h (8 for wavefunction fields, 4 for promolecular fields) */
+/* Same decomposition one level finer, for the one-process-per-GPU model whose gather is a reduce over full arrays: the
+   interleaved unit is one row of super-tiles of a layer (layer_height planes x layer_height lines along y), unit index
+   = layer * ceil(nn2 / layer_height) + row, dealt round-robin like the layers.  50 layers over 8 GPUs leave 7 against
+   6.25 layers per GPU; 2 500 rows leave 313 against 312.5. */
+int c2gpu_eval_grid_dev_part_rows(void *h, const double x0[3], const double xd[9], const int nn[3], int nder,
+                                  int periodic, unsigned outmask, double *const *out_dev, int part, int nparts,
+                                  void *stream);
 int c2gpu_layer_height(void *h);
 
 /* ---- NCIPLOT: evaluation loop src/nci@proc.f90:499-561, cutoff pass :569-604 ---------------------------------- */

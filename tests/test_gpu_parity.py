@@ -91,6 +91,40 @@ def test_cube_synthetic_all_configs(G, O, cfg, variant):
     print(cfg, variant, _compare_cube(got, ref))
 
 
+@pytest.mark.parametrize("cfg", [3, 6])
+def test_interleaved_parts_tile_the_grid(G, cfg):
+    """c2gpu_eval_grid_dev_part / _part_rows: the parts are disjoint, cover the grid and reproduce the one-launch result
+    bit for bit (the multi-GPU decomposition, here on one device)."""
+    import torch
+    from critic2_b200 import synth
+    f = synth.small_synthetic()
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, (21, 19, 26), margin=3.0)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    npt = int(np.prod(nn))
+    props = ("f", "gx", "lap")
+    full = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in props]
+    fld.cube_dev(x0, xd, nn, full, props)
+    for rows in (False, True):
+        acc = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in props]
+        cover = torch.zeros(npt, dtype=torch.float64, device="cuda")
+        for part in range(3):
+            outs = [torch.full((npt,), float("nan"), dtype=torch.float64, device="cuda") for _ in props]
+            fld.cube_dev_part(x0, xd, nn, outs, props, part, 3, rows=rows)
+            torch.cuda.synchronize()
+            own = ~torch.isnan(outs[0])
+            cover += own.double()
+            for a_, o_ in zip(acc, outs):
+                a_ += torch.nan_to_num(o_, nan=0.0)
+        assert bool((cover == 1.0).all()), "parts must be disjoint and cover the grid"
+        for a_, f_ in zip(acc, full):
+            assert torch.equal(a_, f_)
+
+
 @pytest.mark.parametrize("cfg", [3, 6, 7])
 def test_point_lists_through_every_kernel_family(G, O, cfg):
     """c2gpu_eval_points (ragged list: 1 000 points is not a multiple of any tile) through the block-synchronous, the
