@@ -14,6 +14,17 @@ def rank_layers(nslow: int, lh: int, rank: int, world: int):
     return [(L * lh, min(nslow, (L + 1) * lh)) for L in range(rank, nl, world)]
 
 
+def rank_rows(nslow: int, nmid: int, lh: int, rank: int, world: int):
+    """The finer decomposition of c2gpu_eval_grid_dev_part_rows: [(c0, c1, b0, b1)] blocks owned by `rank`, one per row
+    of super-tiles: unit = layer * ceil(nmid / lh) + row, unit mod world == rank (common.cuh part_item)."""
+    nl, nr = (nslow + lh - 1) // lh, (nmid + lh - 1) // lh
+    out = []
+    for u in range(rank, nl * nr, world):
+        L, r = divmod(u, nr)
+        out.append((L * lh, min(nslow, (L + 1) * lh), r * lh, min(nmid, (r + 1) * lh)))
+    return out
+
+
 def rank_points(nslow: int, lh: int, rank: int, world: int, plane_points: int) -> int:
     return sum(c1 - c0 for c0, c1 in rank_layers(nslow, lh, rank, world)) * plane_points
 

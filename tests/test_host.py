@@ -128,6 +128,23 @@ def _gloo_worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
+def test_rank_rows_tile_the_grid():
+    from critic2_b200 import sharding
+    for (nslow, nmid, lh, world) in ((400, 400, 8, 8), (26, 19, 8, 3), (5, 3, 8, 4), (64, 70, 4, 5)):
+        seen = np.zeros((nslow, nmid), int)
+        sizes = []
+        for r in range(world):
+            blocks = sharding.rank_rows(nslow, nmid, lh, r, world)
+            sizes.append(sum((c1 - c0) * (b1 - b0) for c0, c1, b0, b1 in blocks))
+            for c0, c1, b0, b1 in blocks:
+                seen[c0:c1, b0:b1] += 1
+        assert (seen == 1).all()
+        if nslow == 400:   # the bench grid: 2 500 rows over 8 ranks, against 7 vs 6 whole layers
+            assert max(sizes) / (sum(sizes) / world) < 1.002
+            lay = [sharding.rank_points(nslow, lh, r, world, nmid) for r in range(world)]
+            assert max(lay) / (sum(lay) / world) > 1.1
+
+
 def test_two_rank_gather_and_reduction_over_gloo():
     import torch.multiprocessing as mp
     s = socket.socket()
