@@ -71,6 +71,10 @@ struct Replica {
   int *acache_nz = nullptr;
   double *ws_rec = nullptr;
   int acache_chunks = 0;
+  // device output arrays of the host-array drivers, kept between calls (CUBE is typically issued once per property and
+  // NCIPLOT evaluates crho/cgrad/rhoat on the same lattice): freed with the handle
+  std::vector<double *> outbuf;
+  size_t outbuf_n = 0;
 };
 
 struct Handle {
@@ -156,6 +160,7 @@ int c2gpu_destroy(void *handle) {
   for (auto &r : h->reps) {
     DevGuard gd(r.dev);
     for (void *p : r.allocs) cudaFree(p);
+    for (double *p : r.outbuf) cudaFree(p);
     if (r.stream) cudaStreamDestroy(r.stream);
   }
   delete h;

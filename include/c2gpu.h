@@ -76,7 +76,9 @@ int c2gpu_destroy(void *handle);
 /* ---- CUBE: rhoplot_cube evaluation loop, src/rhoplot@proc.f90:582-631 ---------------------------------------- */
 /* property bits of outmask = nti of :488-523: 0 f, 1 gx, 2 gy, 3 gz, 4 gmod, 5 hxx, 6 hxy, 7 hxz, 8 hyy, 9 hyz,
    10 hzz, 11 lap.  out[] holds one nn1*nn2*nn3 array per set bit (ascending bit order), x fastest (lf(ix,iy,iz)).
-   xd: column-major step vectors.  nder is 2 in the reference's loop (:595); 0/1 are accepted (grd semantics). */
+   xd: column-major step vectors.  nder is 2 in the reference's loop (:595); 0/1 are accepted (grd semantics).
+   The host-array entries (this one, c2gpu_nci_grid, c2gpu_promol_grid) keep their device output arrays in the handle
+   between calls (the reference issues one CUBE per property on the same lattice); c2gpu_destroy frees them. */
 #define C2GPU_NPROP 12
 int c2gpu_eval_grid(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
                     unsigned outmask, double *const *out);
