@@ -149,14 +149,22 @@ def test_point_lists_through_every_kernel_family(G, O, cfg):
     assert np.array_equal(got[:, 15] != 0, ref[:, 15] != 0) and np.all(got[:3, 1:4] == 0.0)
 
 
+@pytest.mark.parametrize("cfg", [-1, 3, 6])
 @pytest.mark.parametrize("nder", [0, 1])
-def test_lower_nder(G, O, nder):
+def test_lower_nder(G, O, nder, cfg):
+    """nder = 0 / 1 (grd0, LINE/PLANE of f and gradient components): the ND = 1 and ND = 4 instantiations of the default,
+    the block-synchronous and the warp-specialised kernels."""
     f = cases.golden_wfn("benzene-adz")
     st = cases.mol_structure(f)
     x0, xd, nn = cases.bbox_grid(st, 12, margin=2.0)
     pts = np.array([x0 + xd @ np.array([i, j, k], float) for k in range(nn[2]) for j in range(nn[1]) for i in range(nn[0])])
     ref = _ofield(O, f, st).grd_points(pts, nder=nder, periodic=False)
-    got = G.WfnField(f, st).cube(x0, xd, nn, nder=nder)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    got = fld.cube(x0, xd, nn, nder=nder)
     check_rho(got["f"].reshape(-1), ref[:, 0])
     if nder == 1:
         check_vec(np.stack([got[k].reshape(-1) for k in ("gx", "gy", "gz")], -1), ref[:, 1:4], "grad", rho=ref[:, 0])
