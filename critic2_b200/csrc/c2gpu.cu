@@ -75,6 +75,9 @@ struct Replica {
   // NCIPLOT evaluates crho/cgrad/rhoat on the same lattice): freed with the handle
   std::vector<double *> outbuf;
   size_t outbuf_n = 0;
+  // scratch of the core pre-pass (f%usecore): nd raw sums per point of the evaluated range, grow-only
+  double *corebuf = nullptr;
+  size_t corebuf_n = 0;
 };
 
 struct Handle {
@@ -83,6 +86,7 @@ struct Handle {
   int cfg = 0;    // wavefunction kernel configuration
   int natom = 0, npri = 0, nshell = 0, nmo = 0, nblk = 0;
   std::vector<Replica> reps;
+  Handle *core = nullptr;   // f%usecore: promolecular handle over the core tables (c2gpu_field_set_core); not owned
 };
 
 template <class T>
@@ -161,9 +165,25 @@ int c2gpu_destroy(void *handle) {
     DevGuard gd(r.dev);
     for (void *p : r.allocs) cudaFree(p);
     for (double *p : r.outbuf) cudaFree(p);
+    if (r.corebuf) cudaFree(r.corebuf);
     if (r.stream) cudaStreamDestroy(r.stream);
   }
   delete h;
+  return 0;
+}
+
+int c2gpu_field_set_core(void *handle, void *hcore) {
+  Handle *h = static_cast<Handle *>(handle), *c = static_cast<Handle *>(hcore);
+  if (!h || (h->kind != 1 && h->kind != 2)) return fail(1, "c2gpu_field_set_core: invalid field handle");
+  if (c && c->kind != 2) return fail(1, "c2gpu_field_set_core: the core handle must be a promolecular handle");
+  if (c == h) return fail(1, "c2gpu_field_set_core: a field cannot be its own core");
+  if (c)
+    for (const Replica &r : h->reps) {
+      bool found = false;
+      for (const Replica &rc : c->reps) found = found || rc.dev == r.dev;
+      if (!found) return fail(1, "c2gpu_field_set_core: the core handle is not resident on every device of the field");
+    }
+  h->core = c;
   return 0;
 }
 

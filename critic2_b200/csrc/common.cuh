@@ -31,7 +31,19 @@ struct GridDesc {
   const double *pts;  // non-null: explicit point list (n[0] points, n[1]=n[2]=1), 3 doubles per point
   int ta, tb, tc;  // sub-tile shape (ta*tb*tc = points per tile)
   int sa, sb, sc;  // super-tile shape (multiples of the sub-tile shape)
+  // Ownership filter of the core pre-pass (see OutDesc::core): this launch covers every tile of [c0,c1) but a tile is
+  // evaluated only if the unit of ANOTHER decomposition (layers of height own_sc / rows of own_sb lines, own_ntb rows per
+  // layer, dealt round-robin like c_part/c_nparts/part_rows) that contains it belongs to own_part.  own_nparts <= 1: off.
+  int own_sb, own_sc, own_ntb, own_part, own_nparts, own_rows;
 };
+
+// true if the tile whose first point has output coordinates (b0, c0t) is evaluated under the ownership filter
+__host__ __device__ inline bool tile_owned(const GridDesc &g, int b0, int c0t) {
+  if (g.own_nparts <= 1) return true;
+  const int layer = (c0t - g.c0) / g.own_sc;
+  const int unit = g.own_rows ? layer * g.own_ntb + b0 / g.own_sb : layer;
+  return unit % g.own_nparts == g.own_part;
+}
 
 // Work item `st` of this part -> (super-)tile indices along a, b and the layer index along c (nta, ntb tiles along a, b).
 __host__ __device__ inline void part_item(const GridDesc &g, int st, int nta, int ntb, int &ia, int &ib, int &ic) {
@@ -53,13 +65,21 @@ __host__ __device__ inline int grid_nc(const GridDesc &g) { return g.nci_order ?
 
 // Output selection.  mode 0: CUBE properties (one array per set bit of outmask, src/rhoplot@proc.f90:596-621);
 // mode 1: NCIPLOT crho/cgrad (src/nci@proc.f90:523-525,553-554); mode 2: point list, C2GPU_RES_LEN doubles per point;
-// mode 3: value only into prop[0] (grd0, src/fieldmod@proc.f90:848-928).
+// mode 3: value only into prop[0] (grd0, src/fieldmod@proc.f90:848-928);
+// mode 4: the raw sums f, gf(3), hs(6) before the tail of grd, component k of point idx at res[k*core_stride + idx]
+//         (k < core_nd) -- the core pre-pass below writes this.
+// core != null: f%usecore (src/fieldmod@proc.f90:827-832, :922-925): the core promolecular density and derivatives of
+// the same lattice, written by a mode-4 pre-pass of the promolecular kernel over the core tables cgrid(iz,zpsp(iz)),
+// are added to f, gf, hf BEFORE the nucleus test / gfmod / del2f and the NCIPLOT formulas.
 struct OutDesc {
   int mode;
   unsigned outmask;
   double *prop[12];
   double *crho, *cgrad;
   double *res;
+  const double *core;
+  size_t core_stride;
+  int core_nd;
 };
 
 #ifdef __CUDACC__

@@ -74,14 +74,17 @@ __device__ inline int eig3_ref(const double *h, double *ev) {
   e[1] = e[2];
   e[2] = 0.0;
   double f = 0.0, b = 0.0;
+  // every loop below has compile-time bounds (with predicates) so that d[] and e[] stay in registers
+#pragma unroll
   for (int l = 0; l < 3; l++) {
     int j = 0;
     double hh = amach * (fabs(d[l]) + fabs(e[l]));
     if (b < hh) b = hh;
-    int m;
-    for (m = l; m < 3; m++)
-      if (fabs(e[m]) <= b) break;
-    if (m != l) {
+    int m = 3;
+#pragma unroll
+    for (int mm = 2; mm >= 0; mm--)
+      if (mm >= l && fabs(e[mm]) <= b) m = mm;   // first m >= l with |e(m)| <= b (e[2] = 0 always qualifies)
+    if (l < 2 && m != l) {   // l = 2: m = 2 always (e[2] = 0)
       do {
         if (j == 30) return l + 1;
         j++;
@@ -90,11 +93,15 @@ __device__ inline int eig3_ref(const double *h, double *ev) {
         double r = (fabs(p * amach) > 1.0) ? p : sqrt(p * p + 1.0);
         d[l] = e[l] / (p + copysign(r, p));
         hh = g - d[l];
-        for (int i = l + 1; i < 3; i++) d[i] = d[i] - hh;
+#pragma unroll
+        for (int i = 1; i < 3; i++)
+          if (i >= l + 1) d[i] = d[i] - hh;
         f = f + hh;
-        p = d[m];
+        p = (m == 2) ? d[2] : (m == 1 ? d[1] : d[0]);
         double c = 1.0, s = 0.0;
-        for (int i = m - 1; i >= l; i--) {
+#pragma unroll
+        for (int i = 1; i >= 0; i--) {
+          if (i > m - 1 || i < l) continue;
           g = c * e[i];
           hh = c * p;
           if (fabs(p) >= fabs(e[i])) {
@@ -135,18 +142,36 @@ __device__ inline int eig3_ref(const double *h, double *ev) {
 // NCIPLOT per-point formulas (src/nci@proc.f90:523-525, 553-554).  hs = (xx,yy,zz,xy,xz,yz).
 // nci_const = 2*(3*pi^2)^(1/3), evaluated on the host like the reference does at run time (src/nci@proc.f90:86-87).
 __device__ __forceinline__ void emit_point(const OutDesc &o, size_t idx, double f, double gx, double gy, double gz,
-                                           const double *hs, bool isnuc, double nci_const) {
+                                           double h0, double h1, double h2, double h3, double h4, double h5,
+                                           bool isnuc, double nci_const) {
+  const size_t cs = o.core_stride;
+  if (o.mode == 4) {                                                  // raw sums for the core pre-pass
+    double *r = o.res + idx;
+    r[0] = f;
+    if (o.core_nd >= 4) { r[cs] = gx; r[2 * cs] = gy; r[3 * cs] = gz; }
+    if (o.core_nd >= 10) { r[4 * cs] = h0; r[5 * cs] = h1; r[6 * cs] = h2; r[7 * cs] = h3; r[8 * cs] = h4; r[9 * cs] = h5; }
+    return;
+  }
+  if (o.core) {                                                       // src/fieldmod@proc.f90:827-832
+    const double *c = o.core + idx;
+    f = add_rn(f, c[0]);
+    if (o.core_nd >= 4) { gx = add_rn(gx, c[cs]); gy = add_rn(gy, c[2 * cs]); gz = add_rn(gz, c[3 * cs]); }
+    if (o.core_nd >= 10) {
+      h0 = add_rn(h0, c[4 * cs]); h1 = add_rn(h1, c[5 * cs]); h2 = add_rn(h2, c[6 * cs]);
+      h3 = add_rn(h3, c[7 * cs]); h4 = add_rn(h4, c[8 * cs]); h5 = add_rn(h5, c[9 * cs]);
+    }
+  }
   if (isnuc) { gx = 0.0; gy = 0.0; gz = 0.0; }                        // :838
   double gmod = norm2_ref(gx, gy, gz);                                // :839
-  double lap = add_rn(add_rn(hs[0], hs[1]), hs[2]);                   // :840
+  double lap = add_rn(add_rn(h0, h1), h2);                   // :840
   if (o.mode == 0) {
-    const double v[12] = {f, gx, gy, gz, gmod, hs[0], hs[3], hs[4], hs[1], hs[5], hs[2], lap};
+    const double v[12] = {f, gx, gy, gz, gmod, h0, h3, h4, h1, h5, h2, lap};
     int slot = 0;
 #pragma unroll
     for (int nti = 0; nti < 12; nti++)
       if (o.outmask & (1u << nti)) o.prop[slot++][idx] = v[nti];
   } else if (o.mode == 1) {
-    const double hf[9] = {hs[0], hs[3], hs[4], hs[3], hs[1], hs[5], hs[4], hs[5], hs[2]};
+    const double hf[9] = {h0, h3, h4, h3, h1, h5, h4, h5, h2};
     double ev[3];
     eig3_ref(hf, ev);
     const double vsmall = 1e-80;                                      // src/param.F90:27
@@ -156,9 +181,9 @@ __device__ __forceinline__ void emit_point(const OutDesc &o, size_t idx, double 
   } else if (o.mode == 2) {
     double *r = o.res + idx * 16;
     r[0] = f; r[1] = gx; r[2] = gy; r[3] = gz;
-    r[4] = hs[0]; r[5] = hs[3]; r[6] = hs[4];
-    r[7] = hs[3]; r[8] = hs[1]; r[9] = hs[5];
-    r[10] = hs[4]; r[11] = hs[5]; r[12] = hs[2];
+    r[4] = h0; r[5] = h3; r[6] = h4;
+    r[7] = h3; r[8] = h1; r[9] = h5;
+    r[10] = h4; r[11] = h5; r[12] = h2;
     r[13] = gmod; r[14] = lap; r[15] = isnuc ? 1.0 : 0.0;
   } else {
     o.prop[0][idx] = f;

@@ -46,6 +46,7 @@ struct PromolParams {
   int nta, ntb, ntc;   // tile counts
   double nci_const;
   unsigned long long *count;   // optional: number of (point, atom) pairs inside the cutoffs
+  int use_wc;                  // 1: evaluate at wc (the core call, src/fieldmod@proc.f90:828) instead of wcr (:803)
 };
 
 #ifdef __CUDACC__
@@ -118,6 +119,7 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
   const int ta0 = ia * g.ta, tb0 = ib * g.tb, tc0 = g.c0 + ic * g.tc;
   const int a = ta0 + tid % g.ta, b = tb0 + (tid / g.ta) % g.tb, c = tc0 + tid / (g.ta * g.tb);
   const bool valid = a < na && b < nb && c < g.c1;
+  if (!tile_owned(g, tb0, tc0)) return;      // core pre-pass: another part's unit (block-uniform)
 
   const SpcDev *spc = m.spc;
   if (m.nspc <= PROMOL_NSPC) {               // visible after the barriers of the bounding-box reduction below
@@ -130,6 +132,7 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
     double x[3], wc[3];
     grid_point(g, a, b, c, x);
     grd_wrap(p.xf, x, g.periodic, wc, xc);   // xc = wcr (:802)
+    if (p.use_wc) { xc[0] = wc[0]; xc[1] = wc[1]; xc[2] = wc[2]; }
     center_cart(p.xf, xc, nullptr);          // :1242-1243
 #pragma unroll
     for (int d = 0; d < 3; d++) { lo[d] = xc[d]; hi[d] = xc[d]; }
@@ -293,7 +296,7 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
     for (int o = 16; o > 0; o >>= 1) npair += __shfl_xor_sync(~0u, npair, o);
     if (lane == 0 && npair) atomicAdd(p.count, npair);
   }
-  if (valid) emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs, isnuc, p.nci_const);
+  if (valid) emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs[0], hs[1], hs[2], hs[3], hs[4], hs[5], isnuc, p.nci_const);
 }
 #endif
 

@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
             isnuc = isnuc || (ddx * ddx + ddy * ddy + ddz * ddz) < 1e-10;
           }
         }
-        emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs, isnuc, p.nci_const);
+        emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs[0], hs[1], hs[2], hs[3], hs[4], hs[5], isnuc, p.nci_const);
       }
       __syncthreads();   // the epilogue threads are done with s_tot / s_pt before the next sub-tile overwrites them
     }

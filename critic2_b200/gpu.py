@@ -45,6 +45,7 @@ def lib():
         L.c2gpu_launch_count.restype = C.c_long
         L.c2gpu_set_option.argtypes = [C.c_char_p, C.c_int]
         L.c2gpu_destroy.argtypes = [C.c_void_p]
+        L.c2gpu_field_set_core.argtypes = [C.c_void_p, C.c_void_p]
         L.c2gpu_wfn_create.argtypes = [C.c_int, dp, C.c_int, ip, ip, dp, dp, C.c_int, C.c_int, dp, dp, C.c_int, C.c_int,
                                        C.c_int, ip, ip, dp, dp, dp, C.c_int, dp, dp, C.POINTER(C.c_void_p)]
         L.c2gpu_promol_create.argtypes = [C.c_int, C.c_int, dp, ip, ip, C.c_int, ip, ip, dp, dp, dp, dp, dp, dp, dp,
@@ -164,6 +165,13 @@ class _Field:
             self.close()
         except Exception:
             pass
+
+    # -- f%usecore / f%zpsp, fieldmod@proc.f90:154-157,184-199; used by grd :827-832 and grd0 :922-925 ------------
+    def set_core(self, core: "PromolField | None"):
+        """Attach (or detach with None) the core-density field built by ``core_field``: every driver of this field
+        then adds the promolecular core density and its derivatives before the tail of grd."""
+        _check(lib().c2gpu_field_set_core(self.handle, core.handle if core is not None else None))
+        self._core = core   # keep it alive: the library does not own it
 
     # -- rhoplot_cube evaluation loop, rhoplot@proc.f90:582-631 -------------------------------------------------
     def cube(self, x0, xd, nn, props=PROPS, nder: int = 2, periodic: bool = False):
@@ -322,6 +330,18 @@ class PromolField(_Field):
         s = C.c_double(0)
         _check(lib().c2gpu_promol_count_active(self.handle, _d(x0a), _d(xda), _i(nna), int(periodic), C.byref(s)))
         return s.value
+
+
+def core_field(st, core_tables, zpsp) -> PromolField:
+    """The promolecular field of the CORE densities cgrid(iz, zpsp(iz)) (grid1mod@proc.f90:139-164) over the structure's
+    environment.  core_tables: {(Z, q): dict(a,b,r,f,fp,fpp)} as read_db(Z, q) builds them; zpsp: {Z: q}.  Elements with
+    zpsp <= 0 or without core electrons (Z - q <= 0, grid1mod@proc.f90:100) get no table and contribute nothing
+    (environmod@proc.f90:1299)."""
+    tabs = {}
+    for z, q in zpsp.items():
+        if q > 0 and z - q > 0:
+            tabs[int(z)] = core_tables[(int(z), int(q))]
+    return PromolField(st, tabs)
 
 
 class FragmentField(_Field):

@@ -16,7 +16,7 @@ module gpu_interface
   private
 
   public :: gpu_enabled, gpu_init, gpu_end
-  public :: gpu_wfn_handle, gpu_promol_handle, gpu_destroy
+  public :: gpu_wfn_handle, gpu_promol_handle, gpu_set_core, gpu_destroy
   public :: gpu_cube, gpu_nciplot, gpu_nci_cutoffs, gpu_promolecular_grid
 
   logical, save :: gpu_enabled = .false. !< set by the GPU keyword (global@proc.f90, critic_setvariables)
@@ -65,6 +65,11 @@ module gpu_interface
        type(c_ptr), value :: handle
        integer(c_int) :: ierr
      end function c2gpu_destroy
+     function c2gpu_field_set_core(handle,hcore) bind(c,name="c2gpu_field_set_core") result(ierr)
+       import :: c_int, c_ptr
+       type(c_ptr), value :: handle, hcore
+       integer(c_int) :: ierr
+     end function c2gpu_field_set_core
      function c2gpu_eval_grid(h,x0,xd,nn,nder,periodic,outmask,out) bind(c,name="c2gpu_eval_grid") result(ierr)
        import :: c_int, c_double, c_ptr
        type(c_ptr), value :: h
@@ -215,14 +220,19 @@ contains
   end function gpu_wfn_handle
 
   !> Device image of the promolecular field f(0): environment atoms + agrid(:) radial tables.
-  function gpu_promol_handle(c,fr) result(h)
+  !> With zpsp (f%zpsp of a field loaded with CORE/ZPSP) the tables are the core selection cgrid(iz,zpsp(iz)) that
+  !> environ%promolecular uses when iscore (environmod@proc.f90:1252-1253,1295-1299): the handle is then the core
+  !> field to attach with gpu_set_core.
+  function gpu_promol_handle(c,fr,zpsp) result(h)
     use crystalmod, only: crystal
     use fragmentmod, only: fragment
-    use grid1mod, only: agrid
+    use grid1mod, only: agrid, cgrid, grid1
     use global, only: cutrad
     use param, only: maxzat
     type(crystal), intent(in) :: c
     type(fragment), intent(in), optional :: fr
+    integer, intent(in), optional :: zpsp(:)
+    type(grid1), pointer :: g
     type(c_ptr) :: h
     real(c_double), allocatable :: xyz(:,:), a(:), b(:), cut(:), tr(:), tf(:), tfp(:), tfpp(:)
     integer(c_int), allocatable :: ispc(:), cidx(:), zspc(:), ngrid(:)
@@ -246,8 +256,9 @@ contains
        ngrid(is) = 0; a(is) = 0d0; b(is) = 1d0; cut(is) = 0d0
        if (iz > 0 .and. iz <= maxzat) then
           cut(is) = cutrad(iz)
-          if (agrid(iz)%isinit) then
-             ngrid(is) = agrid(iz)%ngrid; a(is) = agrid(iz)%a; b(is) = agrid(iz)%b
+          g => promol_table(iz)
+          if (associated(g)) then
+             ngrid(is) = g%ngrid; a(is) = g%a; b(is) = g%b
           end if
        end if
        ntot = ntot + ngrid(is)
@@ -257,10 +268,11 @@ contains
     do is = 1, c%nspc
        if (ngrid(is) == 0) cycle
        iz = zspc(is)
-       tr(n0+1:n0+ngrid(is)) = agrid(iz)%r(1:ngrid(is))
-       tf(n0+1:n0+ngrid(is)) = agrid(iz)%f(1:ngrid(is))
-       tfp(n0+1:n0+ngrid(is)) = agrid(iz)%fp(1:ngrid(is))
-       tfpp(n0+1:n0+ngrid(is)) = agrid(iz)%fpp(1:ngrid(is))
+       g => promol_table(iz)
+       tr(n0+1:n0+ngrid(is)) = g%r(1:ngrid(is))
+       tf(n0+1:n0+ngrid(is)) = g%f(1:ngrid(is))
+       tfp(n0+1:n0+ngrid(is)) = g%fp(1:ngrid(is))
+       tfpp(n0+1:n0+ngrid(is)) = g%fpp(1:ngrid(is))
        n0 = n0 + ngrid(is)
     end do
     if (present(fr)) then
@@ -276,7 +288,30 @@ contains
        a,b,cut,tr,tf,tfp,tfpp,merge(1_c_int,0_c_int,c%ismolecule),c%m_x2c,c%m_c2x,c%m_xr2c,c%m_c2xr,pmask,h)
     if (ierr == -1) h = c_null_ptr
     call gpu_check("gpu_promol_handle",ierr)
+  contains
+    !> agrid(iz), or cgrid(iz,zpsp(iz)) for the core field; null() if not initialised or without electrons
+    !> (interp returns 0 when z - qat <= 0, grid1mod@proc.f90:100)
+    function promol_table(iz) result(g)
+      integer, intent(in) :: iz
+      type(grid1), pointer :: g
+      g => null()
+      if (present(zpsp)) then
+         if (.not.allocated(cgrid)) return
+         if (zpsp(iz) <= 0 .or. zpsp(iz) >= iz) return
+         if (cgrid(iz,zpsp(iz))%isinit) g => cgrid(iz,zpsp(iz))
+      else
+         if (agrid(iz)%isinit) g => agrid(iz)
+      end if
+    end function promol_table
   end function gpu_promol_handle
+
+  !> f%usecore (fieldmod@proc.f90:827-832, :922-925): attach the core field (gpu_promol_handle(c,zpsp=f%zpsp)) to the
+  !> handle of field f; every GPU driver then adds the core density and derivatives before the tail of grd.
+  !> Call from field_new/field_set_options after the handle exists, when f%usecore .and. any(f%zpsp > 0).
+  subroutine gpu_set_core(h,hcore)
+    type(c_ptr), intent(in) :: h, hcore
+    call gpu_check("gpu_set_core",c2gpu_field_set_core(h,hcore))
+  end subroutine gpu_set_core
 
   subroutine gpu_destroy(h)
     type(c_ptr), intent(inout) :: h

@@ -72,6 +72,16 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
                         int ismolecule, const double *m_x2c, const double *m_c2x, const double *m_xr2c,
                         const double *m_c2xr, const unsigned char *fragmask, void **handle);
 int c2gpu_destroy(void *handle);
+/*
+ * Core augmentation of a field loaded with the CORE / ZPSP options (f%usecore, f%zpsp: src/fieldmod.f90:64,79,
+ * src/fieldmod@proc.f90:154-157,184-199): grd adds the promolecular CORE density and its derivatives, evaluated at wc
+ * from the tables cgrid(iz,zpsp(iz)) (src/grid1mod@proc.f90:139-164), before the nucleus test / gfmod / del2f
+ * (src/fieldmod@proc.f90:827-832; grd0 :922-925).  hcore is a promolecular handle made by c2gpu_promol_create over the
+ * same environment with the core tables (ngrid[s] = 0 for species with zpsp <= 0 or Z - zpsp <= 0, which contribute
+ * nothing: src/environmod@proc.f90:1299, src/grid1mod@proc.f90:100); NULL detaches.  The core handle is not owned by the
+ * field: destroy it after the field.  Every driver of this header (CUBE, NCIPLOT, point lists) then includes the core.
+ */
+int c2gpu_field_set_core(void *handle, void *hcore);
 
 /* ---- CUBE: rhoplot_cube evaluation loop, src/rhoplot@proc.f90:582-631 ---------------------------------------- */
 /* property bits of outmask = nti of :488-523: 0 f, 1 gx, 2 gy, 3 gz, 4 gmod, 5 hxx, 6 hxy, 7 hxz, 8 hyy, 9 hyz,

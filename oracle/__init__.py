@@ -103,7 +103,7 @@ def _colmajor(m):
 
 class _OrcField(C.Structure):
     _fields_ = [("type", C.c_int), ("env", C.c_void_p), ("wfn", C.c_void_p), ("agrid", C.POINTER(C.c_void_p)),
-                ("fragmask", C.c_char_p)]
+                ("fragmask", C.c_char_p), ("cgrid", C.POINTER(C.c_void_p))]
 
 
 RES_LEN = 30
@@ -130,14 +130,15 @@ class Environ:
 
 
 class Grid1Set:
-    """agrid(:) -- radial tables indexed by atomic number. tables: {Z: dict(a,b,r,f,fp,fpp)}"""
+    """agrid(:) -- radial tables indexed by atomic number. tables: {Z: dict(a,b,r,f,fp,fpp[,q])}; with q = zpsp(Z) > 0
+    the set is the core selection cgrid(Z, zpsp(Z)) that grd's core augmentation uses."""
 
     def __init__(self, tables):
         self.arr = (C.c_void_p * 119)()
         self.ptrs = []
         for z, t in tables.items():
             r, f, fp, fpp = (_f64(t[k]) for k in ("r", "f", "fp", "fpp"))
-            p = lib().orc_grid1_from_table(int(z), 0, len(r), float(t["a"]), float(t["b"]), _d(r), _d(f), _d(fp), _d(fpp))
+            p = lib().orc_grid1_from_table(int(z), int(t.get("q", 0)), len(r), float(t["a"]), float(t["b"]), _d(r), _d(f), _d(fp), _d(fpp))
             self.arr[int(z)] = p
             self.ptrs.append(p)
 
@@ -198,11 +199,13 @@ class Wfn:
 class Field:
     """orc_field: type_wfn (wfn given) or type_promol (grids given)"""
 
-    def __init__(self, env: Environ, wfn: Wfn | None = None, grids: Grid1Set | None = None, fragmask=None):
-        self.env, self.wfn, self.grids = env, wfn, grids
+    def __init__(self, env: Environ, wfn: Wfn | None = None, grids: Grid1Set | None = None, fragmask=None,
+                 core: Grid1Set | None = None):
+        self.env, self.wfn, self.grids, self.core = env, wfn, grids, core
         self._frag = None if fragmask is None else np.ascontiguousarray(fragmask, np.uint8).tobytes()
         self.c = _OrcField(0 if wfn is not None else 1, env.ptr, wfn.ptr if wfn is not None else None,
-                           grids.arr if grids is not None else None, self._frag)
+                           grids.arr if grids is not None else None, self._frag,
+                           core.arr if core is not None else None)
 
     @property
     def ref(self):

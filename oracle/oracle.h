@@ -109,6 +109,9 @@ typedef struct orc_field {
   const orc_wfn *wfn;
   orc_grid1 *const *agrid;
   const unsigned char *fragmask; /* type_promol_frag */
+  /* f%usecore with f%zpsp (src/fieldmod.f90:64,79): the core tables cgrid(iz,zpsp(iz)) indexed by atomic number
+     (NULL entry: zpsp(iz) <= 0, no core for that element); NULL array = usecore off.  grd :827-832, grd0 :922-925 */
+  orc_grid1 *const *cgrid;
 } orc_field;
 /* scalar_value subset (src/types.f90:113-148): res[0]=f, [1..3]=gf, [4..12]=hf (col-major), [13]=gfmod,
    [14]=del2f, [15]=isnuc, [16]=fval, [17]=gkin, [18]=vir, [19..27]=stress, [28..29]=fspin */

@@ -50,6 +50,13 @@ void orc_grd(const orc_field *f, const double *v, int nder, int periodic, double
     orc_promolecular(f->env, f->agrid, wcr, nder, f->fragmask, &res[0], gf, hf);
     res[16] = res[0];
   }
+  if (f->cgrid) {                                               /* :827-832 core augmentation, evaluated at wc */
+    double rho, grad[3], h[9];
+    orc_promolecular(f->env, f->cgrid, wc, nder, NULL, &rho, grad, h);
+    res[0] = res[0] + rho;
+    for (int k = 0; k < 3; k++) gf[k] = gf[k] + grad[k];
+    for (int k = 0; k < 9; k++) hf[k] = hf[k] + h[k];
+  }
   int nid = orc_identify_atom(f->env, wc, 1e-5);                /* :836 */
   res[15] = (nid > 0);
   if (nid > 0) gf[0] = gf[1] = gf[2] = 0.0;                      /* :838 */
@@ -61,13 +68,18 @@ void orc_grd(const orc_field *f, const double *v, int nder, int periodic, double
 double orc_grd0(const orc_field *f, const double *v, int periodic) {
   double wc[3], wcr[3];
   grd_points(f->env, v, periodic, wc, wcr);
+  double rho, g[3], h[9];
   if (f->type == ORC_TYPE_WFN) {
     double o[91];
     orc_rho2(f->wfn, f->env, wcr, 0, o);
-    return o[0];
+    rho = o[0];
+  } else
+    orc_promolecular(f->env, f->agrid, wcr, 0, f->fragmask, &rho, g, h);
+  if (f->cgrid) {                                               /* :922-925 */
+    double rhoaux;
+    orc_promolecular(f->env, f->cgrid, wc, 0, NULL, &rhoaux, g, h);
+    rho = rho + rhoaux;
   }
-  double rho, g[3], h[9];
-  orc_promolecular(f->env, f->agrid, wcr, 0, f->fragmask, &rho, g, h);
   return rho;
 }
 

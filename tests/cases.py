@@ -31,6 +31,17 @@ def tables():
     return out
 
 
+def core_tables():
+    """{(Z, zpsp): table} for C 4, N 5, O 6, Si 4 (tools/make_golden.py)"""
+    d = np.load(os.path.join(GOLDEN, "core_tables.npz"))
+    out = {}
+    for z, q in ((6, 4), (7, 5), (8, 6), (14, 4)):
+        out[(z, q)] = {k: (d[f"{z}_{q}_{k}"] if d[f"{z}_{q}_{k}"].ndim else float(d[f"{z}_{q}_{k}"]))
+                       for k in ("a", "b", "r", "f", "fp", "fpp")}
+        out[(z, q)]["q"] = q
+    return out
+
+
 def mol_structure(f: Molwfn, border=None):
     return structure.molecular_cell(f.xyz, f.z) if border is None else structure.molecular_cell(f.xyz, f.z, border)
 

@@ -449,3 +449,100 @@ def test_promolecular_molecule_fragment(G, O):
         ref = of.cube(x0, xd, nn)
         got = G.PromolField(st, tabs, fragmask=fm).cube(x0, xd, nn)
         _compare_cube(got, ref)
+
+
+def _core_fields(G, O, f, st, zpsp, promol_main=False):
+    """(GPU field with its core attached, oracle field with the same core tables)"""
+    ct = cases.core_tables()
+    core = G.core_field(st, ct, zpsp)
+    otabs = {z: ct[(z, q)] for z, q in zpsp.items() if q > 0}
+    env = O.Environ(st)
+    if promol_main:
+        fld = G.PromolField(st, cases.tables())
+        of = O.Field(env, grids=O.Grid1Set(cases.tables()), core=O.Grid1Set(otabs))
+    else:
+        fld = G.WfnField(f, st)
+        of = O.Field(env, wfn=O.Wfn(f), core=O.Grid1Set(otabs))
+    fld.set_core(core)
+    return fld, of
+
+
+@pytest.mark.parametrize("cfg", [-1, 3, 6])
+def test_core_augmented_cube_points_and_nci(G, O, cfg):
+    """LOAD ... CORE ZPSP: grd adds the promolecular core density (fieldmod@proc.f90:827-832) before the nucleus test,
+    gfmod / del2f and the NCIPLOT formulas; through the small-MO, block-synchronous and warp-specialised kernels."""
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld, of = _core_fields(G, O, f, st, {6: 4, 1: 0})
+    finally:
+        G.set_option("wfn_cfg", -1)
+    x0, xd, nn = cases.bbox_grid(st, (23, 21, 18), margin=2.0)
+    ref = of.cube(x0, xd, nn)
+    plain = _ofield(O, f, st).cube(x0, xd, nn)
+    assert np.abs(ref["f"] - plain["f"]).max() > 1e-2          # the core really contributes on this lattice
+    _compare_cube(fld.cube(x0, xd, nn), ref)
+    for nder in (0, 1):                                        # grd0-like and gradient-only passes carry the core too
+        got = fld.cube(x0, xd, nn, props=("f", "gx", "gy", "gz", "gmod"), nder=nder)
+        check_rho(got["f"], ref["f"])
+        if nder:
+            check_vec(np.stack([got[k] for k in ("gx", "gy", "gz")], -1),
+                      np.stack([ref[k] for k in ("gx", "gy", "gz")], -1), "grad", rho=ref["f"])
+    # point list incl. the nuclei (gradient nullified after the core is added)
+    rng = np.random.default_rng(5)
+    pts = np.concatenate([st.r[:3], st.r[0] + rng.uniform(-1.0, 1.0, (300, 3))])
+    rres = of.grd_points(pts, 2, True)
+    res = fld.points(pts, 2, True)
+    assert np.array_equal(res[:, 15], rres[:, 15]) and res[:3, 15].all() and not res[:3, 1:4].any()
+    check_rho(res[:, 0], rres[:, 0])
+    check_vec(res[:, 1:4], rres[:, 1:4], "grad", rho=rres[:, 0])
+    check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])
+    # NCIPLOT on the augmented field
+    x0n, xmat, ns = drivers.nci_grid(st, nstep=(18, 17, 16))
+    rrho, rgrad, _ = of.nci(x0n, xmat, ns)
+    crho, cgrad, _ = fld.nci(x0n, xmat, ns)
+    assert _nci_compare(crho, cgrad, rrho, rgrad) == 0
+    # detaching restores the valence-only field
+    fld.set_core(None)
+    check_rho(fld.cube(x0, xd, nn, props=("f",))["f"], plain["f"])
+
+
+def test_core_prepass_follows_the_interleaved_parts(G):
+    """The core pre-pass only evaluates the tiles of the units a part owns; the parts still tile the grid bit for bit."""
+    import torch
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    G.set_option("wfn_cfg", 3)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    fld.set_core(G.core_field(st, cases.core_tables(), {6: 4}))
+    x0, xd, nn = cases.bbox_grid(st, (26, 21, 19), margin=2.0)
+    npt = int(np.prod(nn))
+    props = ("f", "gmod", "lap")
+    full = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in props]
+    fld.cube_dev(x0, xd, nn, full, props)
+    for rows in (False, True):
+        acc = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in props]
+        for part in range(3):
+            outs = [torch.full((npt,), float("nan"), dtype=torch.float64, device="cuda") for _ in props]
+            fld.cube_dev_part(x0, xd, nn, outs, props, part, 3, rows=rows)
+            torch.cuda.synchronize()
+            for a_, o_ in zip(acc, outs):
+                a_ += torch.nan_to_num(o_, nan=0.0)
+        for a_, f_ in zip(acc, full):
+            assert torch.equal(a_, f_)
+
+
+def test_core_on_a_promolecular_crystal_field(G, O):
+    """usecore on a type_promol field in a periodic cell (quartz, Si zpsp 4, O zpsp 6): the core call uses wc, the
+    valence call wcr (fieldmod@proc.f90:803,828); both are folded by y2z_center."""
+    st = cases.quartz(1)
+    fld, of = _core_fields(G, O, None, st, {14: 4, 8: 6}, promol_main=True)
+    from critic2_b200 import drivers
+    o, xd, nn = drivers.cube_grid(st, (18, 17, 20))
+    ref = of.cube(o, xd, nn, periodic=True)
+    _compare_cube(fld.cube(o, xd, nn, periodic=True), ref)

@@ -298,3 +298,38 @@ def test_cube_loop_matches_point_calls_and_layout():
     assert crho.shape == (5, 4, 3)
     r = fld.grd(x0 + xd @ np.array([4, 1, 2], float), 2, True)
     assert abs(abs(crho[4, 1, 2]) - 100 * r[0]) <= 1e-13 * 100 * r[0]
+
+
+@pytest.mark.parametrize("z,q", [(6, 4), (8, 6), (14, 4)])
+def test_core_tables_integrate_to_the_core_charge(z, q):
+    """cgrid(Z, zpsp) = read_db(Z, q) keeps the first Z - q electrons of the configuration (grid1mod@proc.f90:240-251)."""
+    t = cases.core_tables()[(z, q)]
+    r, fv = t["r"], t["f"]
+    n = np.trapezoid(4 * np.pi * r ** 3 * fv, np.log(r))
+    assert abs(n - (z - q)) < 2e-3 * (z - q)
+    assert r[-1] < cases.tables()[z]["r"][-1]          # truncated where the core density falls under 1e-8 (:260)
+
+
+def test_core_augmentation_of_grd_and_grd0():
+    """f%usecore: grd = valence field + promolecular core (fieldmod@proc.f90:827-832) before the nucleus test and the
+    gfmod / del2f tail; grd0 adds the value only (:922-925)."""
+    f = cases.golden_wfn("h2o-aqz")
+    st = cases.mol_structure(f)
+    env = oracle.Environ(st)
+    ct = cases.core_tables()
+    core = oracle.Grid1Set({8: ct[(8, 6)]})
+    plain = oracle.Field(env, wfn=oracle.Wfn(f))
+    aug = oracle.Field(env, wfn=oracle.Wfn(f), core=core)
+    only = oracle.Field(env, grids=core)               # the core tables as a promolecular field of their own
+    rng = np.random.default_rng(3)
+    pts = st.r[0] + rng.uniform(-0.6, 0.6, (40, 3))    # inside the oxygen core radius (1.7 bohr) and around it
+    a, b, c = plain.grd_points(pts, 2), aug.grd_points(pts, 2), only.grd_points(pts, 2)
+    assert np.abs(c[:, 0]).max() > 1.0 and np.abs(c[:, 0]).min() > 0.0
+    np.testing.assert_allclose(b[:, 0:13], a[:, 0:13] + c[:, 0:13], rtol=1e-12, atol=0)
+    np.testing.assert_allclose(b[:, 13], np.linalg.norm(b[:, 1:4], axis=1), rtol=1e-14)
+    np.testing.assert_allclose(b[:, 14], b[:, 4] + b[:, 8] + b[:, 12], rtol=1e-14)
+    far = st.r[0] + np.array([[3.0, 0.5, -0.2]])       # beyond the core table: the augmentation is exactly zero
+    assert np.array_equal(plain.grd_points(far, 2)[:, :15], aug.grd_points(far, 2)[:, :15])
+    # on the nucleus the gradient (valence + core) is nullified (:836-838)
+    nuc = aug.grd(st.r[0], 2, True)
+    assert nuc[15] == 1.0 and np.all(nuc[1:4] == 0.0) and nuc[0] > plain.grd(st.r[0], 2, True)[0]

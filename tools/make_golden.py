@@ -27,6 +27,16 @@ for z, el in ((1, "h_"), (6, "c_"), (7, "n_"), (8, "o_"), (14, "si")):
     print(el, "ngrid", len(t["r"]), "rmax", t["r"][-1], "a", t["a"], "b", t["b"])
 np.savez_compressed(os.path.join(OUT, "promol_tables.npz"), **tabs)
 
+# core tables cgrid(Z, zpsp) (grid1_register_core -> read_db(Z, q), grid1mod@proc.f90:139-164,57-80): the usual
+# pseudopotential valences C 4, N 5, O 6, Si 4
+ctabs = {}
+for z, q, el in ((6, 4, "c_"), (7, 5, "n_"), (8, 6, "o_"), (14, 4, "si")):
+    t = oracle.read_critic(f"{REF}/dat/wfc/{el}_pbe.wfc", z, q)
+    for k, v in t.items():
+        ctabs[f"{z}_{q}_{k}"] = np.asarray(v)
+    print("core", el, q, "ngrid", len(t["r"]), "rmax", t["r"][-1])
+np.savez_compressed(os.path.join(OUT, "core_tables.npz"), **ctabs)
+
 for name, path, rd in (("h2o-aqz", f"{REF}/tests_cint/h2o-aqz.fchk", wfn.read_fchk),
                        ("benzene-adz", f"{REF}/tests_cint/benzene-adz.fchk", wfn.read_fchk),
                        ("hooh-atz", f"{REF}/tests_cint/hooh-atz.fchk", wfn.read_fchk),
