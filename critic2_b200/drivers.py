@@ -202,6 +202,84 @@ def write_nci_dat(path: str, dat) -> int:
     return len(text)
 
 
+# ---- NCIPLOT checkpoint (.chk_nci): writechk / readchk, nci@proc.f90:962-1059 -------------------------------------
+# gfortran unformatted sequential records: <int32 nbytes> payload <int32 nbytes>; a record longer than 2^31-9 bytes is
+# split into subrecords whose head marker is negative when another subrecord follows and whose tail marker is negative
+# when one precedes (libgfortran io/unix.c); default LOGICAL and INTEGER are 4 bytes.
+_SUBREC = 2147483639
+
+
+def _f_record(fh, payload) -> None:
+    mv = memoryview(payload).cast("B")
+    n, pos, first = len(mv), 0, True
+    while True:
+        m = min(_SUBREC, n - pos)
+        more = pos + m < n
+        fh.write(np.int32(-m if more else m).tobytes())
+        fh.write(mv[pos:pos + m])
+        fh.write(np.int32(m if first else -m).tobytes())
+        pos, first = pos + m, False
+        if not more:
+            return
+
+
+def _f_read_record(fh) -> bytes:
+    out = []
+    while True:
+        head = int(np.frombuffer(fh.read(4), np.int32)[0])
+        out.append(fh.read(abs(head)))
+        tail = int(np.frombuffer(fh.read(4), np.int32)[0])
+        if abs(tail) != abs(head):
+            raise ValueError("corrupt unformatted record")
+        if head >= 0:
+            return b"".join(out)
+
+
+def write_chk_nci(path: str, x0, xmat, nstep, crho, cgrad, rhoat=None, rhofrag=None) -> None:
+    """writechk (nci@proc.f90:1027-1059).  crho/cgrad/rhoat indexed [i][j][k] (the reference's (k,j,i) memory order),
+    rhofrag [ifr][i][j][k]; xmat[:, i] is the i-th step vector."""
+    nfrag = 0 if rhofrag is None else int(np.asarray(rhofrag).shape[0])
+    xmat = np.asarray(xmat, float)
+    with open(path, "wb") as fh:
+        _f_record(fh, np.array([rhoat is not None, rhofrag is not None, nfrag], np.int32))
+        _f_record(fh, np.ascontiguousarray(x0, float))
+        for i in range(3):
+            _f_record(fh, np.ascontiguousarray(xmat[:, i]))
+        _f_record(fh, np.ascontiguousarray(nstep, np.int32))
+        _f_record(fh, np.concatenate([np.ascontiguousarray(crho, float).reshape(-1),
+                                      np.ascontiguousarray(cgrad, float).reshape(-1)]))
+        if rhoat is not None:
+            _f_record(fh, np.ascontiguousarray(rhoat, float))
+        if rhofrag is not None:
+            _f_record(fh, np.ascontiguousarray(rhofrag, float))
+
+
+def read_chk_nci(path: str, x0, xmat, nstep, want_rhoat: bool = False, nfrag: int = 0):
+    """readchk (nci@proc.f90:962-1024): returns (crho, cgrad, rhoat, rhofrag) or None when the file does not match the
+    current lattice / options (the reference then restarts the evaluation)."""
+    xmat = np.asarray(xmat, float)
+    ns = [int(v) for v in nstep]
+    with open(path, "rb") as fh:
+        llat, llfrag, nfrag0 = (int(v) for v in np.frombuffer(_f_read_record(fh), np.int32))
+        if (not llat and want_rhoat) or (not llfrag and nfrag > 0) or nfrag0 != nfrag:
+            return None
+        chk = [np.asarray(x0, float)] + [xmat[:, i] for i in range(3)]
+        for ref in chk:
+            if np.any(np.abs(np.frombuffer(_f_read_record(fh), np.float64) - ref) > 1e-13):
+                return None
+        if list(np.frombuffer(_f_read_record(fh), np.int32)) != ns:
+            return None
+        npt = ns[0] * ns[1] * ns[2]
+        both = np.frombuffer(_f_read_record(fh), np.float64)
+        crho, cgrad = both[:npt].reshape(ns).copy(), both[npt:].reshape(ns).copy()
+        rhoat = rhofrag = None
+        if llat and want_rhoat:
+            rhoat = np.frombuffer(_f_read_record(fh), np.float64).reshape(ns).copy()
+            if llfrag and nfrag > 0:
+                rhofrag = np.frombuffer(_f_read_record(fh), np.float64).reshape([nfrag] + ns).copy()
+    return crho, cgrad, rhoat, rhofrag
+
+
 # ---- point-list callers of field%grd (SURVEY 8(f) rank 2): LINE, PLANE, mesh fill -----------------------------------
 _RES_OF_NTI = {0: 0, 1: 1, 2: 2, 3: 3, 4: 13, 5: 4, 6: 7, 7: 10, 8: 8, 9: 11, 10: 12, 11: 14}   # res column of nti
 

@@ -160,3 +160,33 @@ def test_two_rank_gather_and_reduction_over_gloo():
     for p in procs:
         p.join(timeout=60)
     assert all(ok for _, ok in res), res
+
+
+def test_chk_nci_checkpoint_round_trip(tmp_path, monkeypatch):
+    """writechk / readchk (nci@proc.f90:962-1059): gfortran unformatted records, including the subrecord split of a
+    record longer than the 2^31-9 byte limit (exercised with a small limit) and the compatibility checks."""
+    from critic2_b200 import drivers
+    rng = np.random.default_rng(2)
+    ns = (5, 4, 3)
+    x0, xmat = rng.normal(size=3), rng.normal(size=(3, 3))
+    crho, cgrad, rhoat = (rng.normal(size=ns) for _ in range(3))
+    rhofrag = rng.normal(size=(2,) + ns)
+    p = str(tmp_path / "a.chk_nci")
+    drivers.write_chk_nci(p, x0, xmat, ns, crho, cgrad, rhoat, rhofrag)
+    raw = open(p, "rb").read()
+    # first record: three 4-byte values between two 4-byte markers of 12
+    assert np.frombuffer(raw[:20], np.int32).tolist() == [12, 1, 1, 2, 12]
+    assert len(raw) == (12 + 8) + 4 * (24 + 8) + (12 + 8) + (2 * 480 + 8) + (480 + 8) + (960 + 8)
+    got = drivers.read_chk_nci(p, x0, xmat, ns, want_rhoat=True, nfrag=2)
+    for a, b in zip(got, (crho, cgrad, rhoat, rhofrag)):
+        assert np.array_equal(a, b)
+    assert drivers.read_chk_nci(p, x0 + 1e-9, xmat, ns, want_rhoat=True, nfrag=2) is None
+    assert drivers.read_chk_nci(p, x0, xmat, (5, 4, 4), want_rhoat=True, nfrag=2) is None
+    assert drivers.read_chk_nci(p, x0, xmat, ns, want_rhoat=True, nfrag=1) is None
+    monkeypatch.setattr(drivers, "_SUBREC", 200)          # force subrecords: 960-byte record -> 5 pieces
+    drivers.write_chk_nci(p, x0, xmat, ns, crho, cgrad)
+    raw = open(p, "rb").read()
+    off = 20 + 4 * 32 + 20
+    assert np.frombuffer(raw[off:off + 4], np.int32)[0] == -200
+    got = drivers.read_chk_nci(p, x0, xmat, ns)
+    assert np.array_equal(got[0], crho) and np.array_equal(got[1], cgrad) and got[2] is None
