@@ -189,6 +189,16 @@ __device__ __forceinline__ void emit_point(const OutDesc &o, size_t idx, double 
     o.prop[0][idx] = f;
   }
 }
+
+// Out-of-line copy for the warp-specialised kernel: its point epilogue runs on 16 threads once per point, and keeping this
+// code (eigenvalue iteration, pow, twelve stores) out of the kernel body keeps the register allocation of the DMMA
+// loops independent of it (measured: inlining a larger emit_point cost 3 % of the whole pass through a different
+// operand-register assignment in the consumer loop).
+static __device__ __noinline__ void emit_point_call(const OutDesc &o, size_t idx, double f, double gx, double gy, double gz,
+                                             double h0, double h1, double h2, double h3, double h4, double h5,
+                                             bool isnuc, double nci_const) {
+  emit_point(o, idx, f, gx, gy, gz, h0, h1, h2, h3, h4, h5, isnuc, nci_const);
+}
 #endif
 
 }  // namespace c2

@@ -613,7 +613,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
             isnuc = isnuc || (ddx * ddx + ddy * ddy + ddz * ddz) < 1e-10;
           }
         }
-        emit_point(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs[0], hs[1], hs[2], hs[3], hs[4], hs[5], isnuc, p.nci_const);
+        emit_point_call(p.o, out_index(g, a, b, c), f, gx, gy, gz, hs[0], hs[1], hs[2], hs[3], hs[4], hs[5], isnuc, p.nci_const);
       }
     }
     if (w.nedf > 0) named_bar_sync(1, NCT);              // EDF scratch (the other s_part buffer) free again

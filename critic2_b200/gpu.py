@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libc2gpu.so")
+LIB_PATH = os.environ.get("C2GPU_LIB") or os.path.join(_HERE, "libc2gpu.so")   # C2GPU_LIB: A/B builds in development
 
 PROPS = ("f", "gx", "gy", "gz", "gmod", "hxx", "hxy", "hxz", "hyy", "hyz", "hzz", "lap")  # rhoplot@proc.f90:488-523
 RES_LEN = 16
