@@ -321,10 +321,24 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
   set_cell(h->xf, ismolecule, m_x2c, m_c2x, m_xr2c, m_c2xr);
   h->natom = nenv;
 
-  // species tables: node-interleaved (r,f,fp,fpp) + reciprocal node differences of every 4-node stencil
+  // species tables: the interpolating cubic of every 4-node stencil (grid1%interp, src/grid1mod@proc.f90:108-133), as
+  // coefficients of (r - xc)^k about the stencil's second node, from Newton divided differences in long double
   std::vector<SpcDev> spc(nspc);
-  std::vector<double4> nodes;
-  std::vector<double> inv;
+  std::vector<double> poly1, poly4, poly10;
+  size_t nnodes = 0;
+  auto cubic = [](const double *x, const double *y, double *c) {
+    const long double x0 = x[0], x1 = x[1], x2 = x[2], x3 = x[3];
+    const long double f01 = ((long double)y[1] - y[0]) / (x1 - x0), f12 = ((long double)y[2] - y[1]) / (x2 - x1),
+                      f23 = ((long double)y[3] - y[2]) / (x3 - x2);
+    const long double f012 = (f12 - f01) / (x2 - x0), f123 = (f23 - f12) / (x3 - x1);
+    const long double a0 = y[0], a1 = f01, a2 = f012, a3 = (f123 - f012) / (x3 - x0);
+    const long double h0 = x1 - x0, h1 = x2 - x1;
+    // p = a0 + a1 (t+h0) + a2 t (t+h0) + a3 t (t+h0) (t-h1),  t = r - x1
+    c[0] = (double)(a0 + a1 * h0);
+    c[1] = (double)(a1 + a2 * h0 - a3 * h0 * h1);
+    c[2] = (double)(a2 + a3 * (h0 - h1));
+    c[3] = (double)a3;
+  };
   size_t off_in = 0;
   double rcutmax = 0.0;
   std::vector<char> used(nspc, 0);
@@ -335,7 +349,7 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
   for (int s = 0; s < nspc; s++) {
     SpcDev &d = spc[s];
     int n = ngrid[s];
-    d.off = (int)nodes.size(); d.n = n; d.z = zspc[s]; d.pad = 0;
+    d.off = (int)nnodes; d.n = n; d.z = zspc[s]; d.pad = 0;
     d.a = a[s]; d.b = b[s]; d.cutrad = cutrad[s];
     d.ln2_b = b[s] != 0.0 ? std::log(2.0) / b[s] : 0.0;
     d.lna_b = (b[s] != 0.0 && a[s] > 0.0) ? std::log(a[s]) / b[s] : 0.0;
@@ -344,18 +358,18 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
       d.rmax = r[n - 1]; d.r1 = r[0];
       d.rcut = std::min(cutrad[s], d.rmax);                    // src/environmod@proc.f90:1257
       for (int k = 0; k < n; k++) {
-        nodes.push_back(make_double4(r[k], tab_f[off_in + k], tab_fp[off_in + k], tab_fpp[off_in + k]));
-        double iv[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (k + 3 < n) {                                       // x1dr12(i,j) = 1/(rr(i)-rr(j)), src/grid1mod@proc.f90:113-116
-          iv[0] = 1.0 / (r[k + 1] - r[k]);
-          iv[1] = 1.0 / (r[k + 2] - r[k]);
-          iv[2] = 1.0 / (r[k + 2] - r[k + 1]);
-          iv[3] = 1.0 / (r[k + 3] - r[k]);
-          iv[4] = 1.0 / (r[k + 3] - r[k + 1]);
-          iv[5] = 1.0 / (r[k + 3] - r[k + 2]);
+        double rec[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        if (k + 3 < n) {
+          rec[0] = r[k + 1];
+          cubic(r + k, tab_f + off_in + k, rec + 1);
+          cubic(r + k, tab_fp + off_in + k, rec + 5);
+          cubic(r + k, tab_fpp + off_in + k, rec + 9);
         }
-        inv.insert(inv.end(), iv, iv + 8);
+        poly1.insert(poly1.end(), rec, rec + 6);     // xc c0 c1 c2 c3 -
+        poly4.insert(poly4.end(), rec, rec + 10);    // ... d0 d1 d2 d3 -
+        poly10.insert(poly10.end(), rec, rec + 14);  // ... e0 e1 e2 e3 -
       }
+      nnodes += (size_t)n;
     } else {
       d.n = 0; d.rmax = 0; d.r1 = 0;
       d.rcut = cutrad[s];                                      // :1259
@@ -410,8 +424,9 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
     rc |= upload(r, atoms, &m.atoms);
     rc |= upload(r, bin_start, &m.bin_start);
     rc |= upload(r, spc, &m.spc);
-    rc |= upload(r, nodes, &m.nodes);
-    rc |= upload(r, inv, &m.inv);
+    rc |= upload(r, poly1, &m.poly1);
+    rc |= upload(r, poly4, &m.poly4);
+    rc |= upload(r, poly10, &m.poly10);
     m.fragmask = nullptr;
     if (fragmask) rc |= upload(r, frag, &m.fragmask);
     void *d = nullptr;

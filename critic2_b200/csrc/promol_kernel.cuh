@@ -7,9 +7,8 @@
 // One CTA per tile of PT points (one thread per point).  The CTA walks the atom bins that can reach the tile's
 // bounding box, keeps (ordered warp-ballot compaction) the atoms whose species cutoff sphere touches the box in a
 // shared-memory list, and every thread sums its point's contributions from that list; the list is flushed in batches
-// so any number of candidates works.  Radial tables are stored node-interleaved (r,f,fp,fpp = one 32-byte sector per
-// node) with the six reciprocal node differences of each 4-node stencil precomputed on the host in the reference's
-// own arithmetic (x1dr12, :108-117).
+// so any number of candidates works.  Each 4-node stencil of the radial tables is stored as its interpolating cubic
+// (expanded on the host in extended precision about the stencil's second node), one 128-byte line per stencil.
 #pragma once
 #include "epilogue.cuh"
 
@@ -32,8 +31,9 @@ struct PromolDev {
   double bin0[3], bin_inv;
   int nbin[3];
   const SpcDev *spc;
-  const double4 *nodes;     // packed (r, f, fp, fpp)
-  const double *inv;        // 8 doubles per stencil base: 1/(r1-r0),1/(r2-r0),1/(r2-r1),1/(r3-r0),1/(r3-r1),1/(r3-r2)
+  // per stencil base the cubic through nodes base..base+3 of each table as sum_k c_k (r - xc)^k, xc = r(base+1):
+  // xc, c0..c3 (f) [, d0..d3 (fp) [, e0..e3 (fpp)]] padded to 6 / 10 / 14 doubles; one table per derivative order
+  const double *poly1, *poly4, *poly10;
   const unsigned char *fragmask;
   double rcutmax;
 };
@@ -79,21 +79,27 @@ __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &
     else ir = 1 + (int)floor(__ddiv_rn(log(__ddiv_rn(r0, s.a)), s.b));
     r = r0;
   }
-  int base = min(max(ir, 2), s.n - 2) - 2;                             // :110, 0-based first node
-  const double4 *nd = m.nodes + s.off + base;
-  const double4 n0 = nd[0], n1 = nd[1], n2 = nd[2], n3 = nd[3];
-  const double4 *iv = reinterpret_cast<const double4 *>(m.inv + 8 * (size_t)(s.off + base));
-  const double4 ia = iv[0], ib = iv[1];
-  const double i10 = ia.x, i20 = ia.y, i21 = ia.z, i30 = ia.w, i31 = ib.x, i32 = ib.y;
-  const double d0 = r - n0.x, d1 = r - n1.x, d2 = r - n2.x, d3 = r - n3.x;
-  // prod_i = prod_{j != i} dr1(j) * x1dr12(i,j), j ascending (:119-126); x1dr12(i,j) = -x1dr12(j,i)
-  double p0 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d1, -i10), d2), -i20), d3), -i30);
-  double p1 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i10), d2), -i21), d3), -i31);
-  double p2 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i20), d1), i21), d3), -i32);
-  double p3 = mul_rn(mul_rn(mul_rn(mul_rn(mul_rn(d0, i30), d1), i31), d2), i32);
-  f = n0.y * p0 + n1.y * p1 + n2.y * p2 + n3.y * p3;
-  if (ND > 1) fp = n0.z * p0 + n1.z * p1 + n2.z * p2 + n3.z * p3;
-  if (ND > 4) fpp = n0.w * p0 + n1.w * p1 + n2.w * p2 + n3.w * p3;
+  const int base = min(max(ir, 2), s.n - 2) - 2;                       // :110, 0-based first node of the stencil
+  // The 4-node Lagrange interpolant (:112-133) is one cubic per stencil: the host expands it once, in extended precision,
+  // about the stencil's second node (PromolDev::poly*), so a pair costs 40 / 72 / 104 bytes of table reads (ND = 1 / 4 / 10)
+  // and three FMAs per interpolated table instead of 192 bytes (four nodes + six reciprocal differences) and 24 multiplies.
+  // The kernel is bound by the L1 data stage of these divergent gathers (ncu: l1tex wavefronts 91-93 % of peak, FP64 pipe
+  // 20-26 %): one table per ND with record strides of 48 / 80 / 112 bytes, so that the 16-byte pieces fetched by the lanes
+  // of a request fall on all eight 16-byte bank groups of a line instead of one (a 128-byte stride serialises them).
+  constexpr int STR = ND == 1 ? 6 : (ND == 4 ? 10 : 14);
+  const double *tab = ND == 1 ? m.poly1 : (ND == 4 ? m.poly4 : m.poly10);
+  const double2 *pc = reinterpret_cast<const double2 *>(tab + STR * (size_t)(s.off + base));
+  const double2 q0 = pc[0], q1 = pc[1], q2 = pc[2];                    // xc c0 | c1 c2 | c3 d0
+  const double t = r - q0.x;
+  f = fma(t, fma(t, fma(t, q2.x, q1.y), q1.x), q0.y);
+  if (ND > 1) {
+    const double2 q3 = pc[3], q4 = pc[4];                              // d1 d2 | d3 e0
+    fp = fma(t, fma(t, fma(t, q4.x, q3.y), q3.x), q2.y);
+    if (ND > 4) {
+      const double2 q5 = pc[5], q6 = pc[6];                            // e1 e2 | e3 -
+      fpp = fma(t, fma(t, fma(t, q6.x, q5.y), q5.x), q4.y);
+    }
+  }
 }
 
 constexpr int PROMOL_PT = 256;    // points per tile = threads per CTA
