@@ -351,12 +351,14 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
     int n = ngrid[s];
     d.off = (int)nnodes; d.n = n; d.z = zspc[s]; d.pad = 0;
     d.a = a[s]; d.b = b[s]; d.cutrad = cutrad[s];
-    d.ln2_b = b[s] != 0.0 ? std::log(2.0) / b[s] : 0.0;
+    d.ln2_b = b[s] >= 1e-3 ? std::log(2.0) / b[s] : std::nan("");   // NaN: the index pre-screen never accepts
     d.lna_b = (b[s] != 0.0 && a[s] > 0.0) ? std::log(a[s]) / b[s] : 0.0;
     if (n >= 4) {
       const double *r = tab_r + off_in;
       d.rmax = r[n - 1]; d.r1 = r[0];
       d.rcut = std::min(cutrad[s], d.rmax);                    // src/environmod@proc.f90:1257
+      d.rmax_lo = d.rmax * (1.0 - 1e-14);
+      d.rfloor = std::max(d.r1, 1e-14);
       for (int k = 0; k < n; k++) {
         double rec[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
         if (k + 3 < n) {
@@ -371,7 +373,7 @@ int c2gpu_promol_create(int nenv, int ncell, const double *xyz_env, const int *i
       }
       nnodes += (size_t)n;
     } else {
-      d.n = 0; d.rmax = 0; d.r1 = 0;
+      d.n = 0; d.rmax = 0; d.r1 = 0; d.rmax_lo = 0; d.rfloor = 1e-14;
       d.rcut = cutrad[s];                                      // :1259
     }
     off_in += (size_t)std::max(n, 0);

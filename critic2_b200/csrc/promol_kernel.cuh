@@ -21,7 +21,10 @@ struct SpcDev {
   double rcut;        // min(cutrad(z), rmax) (:1246-1263); cutrad alone if the table is missing
   double cutrad;
   double rmax, r1;    // last and first node radius
-  double ln2_b, lna_b;   // ln(2)/b and ln(a)/b: the pre-screen of the log-grid index (radial_interp)
+  double ln2_b, lna_b;   // ln(2)/b and ln(a)/b: the pre-screen of the log-grid index (radial_interp); ln2_b = NaN
+                         // when b < 1e-3 (pre-screen margins not valid: every pair takes the reference's own expression)
+  double rmax_lo;        // rmax*(1 - 1e-14): below it r < rmax for certain
+  double rfloor;         // max(r1, 1e-14): the clamp of :1302
 };
 
 struct PromolDev {
@@ -56,16 +59,22 @@ __device__ __forceinline__ void unpack_atom(const double4 &a, int &is, int &cidx
   cidx = (int)(bits >> 32);
 }
 
-// grid1%interp (src/grid1mod@proc.f90:84-135) for r already clamped to >= r(1) by the caller (:1302)
+__device__ __forceinline__ float lg2_approx(float x) {   // MUFU.LG2 without the denormal fix-up (x is in [1,2))
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// grid1%interp (src/grid1mod@proc.f90:84-135) for r0 already clamped to >= r(1) by the caller (:1302) and < rmax (:98 is
+// the caller's job).  r0 = r(1) needs no branch of its own: the index expression gives ir <= 1 there and the stencil base
+// is 0 like in the reference's r0 <= r(1) branch (:103-105), with the same r.
 template <int ND>
 __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &s, double r0, double &f, double &fp,
                                               double &fpp) {
-  f = 0.0; fp = 0.0; fpp = 0.0;
-  if (r0 >= s.rmax) return;                                            // :98
+  fp = 0.0; fpp = 0.0;
   int ir;
-  double r;
-  if (r0 <= s.r1) { ir = 1; r = s.r1; }                                // :103-105
-  else {                                                               // ir = 1 + floor(log(r0/a)/b), :107
+  const double r = r0;
+  {                                                                    // ir = 1 + floor(log(r0/a)/b), :107
     // The FP64 log and the two divisions cost ~55 FP64 instructions per (point, atom) pair.  t = log(r0/a)/b is first
     // estimated as ((e + log2(m)) ln2 - ln a)/b with the mantissa's log2 from the SFU (absolute error <= 2^-22 on
     // [1,2] -> |dt| < 1.3e-4 for b = 0.002); unless t lies within 4e-4 of an integer its floor is already certain,
@@ -73,11 +82,11 @@ __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &
     const long long bits = __double_as_longlong(r0);
     const int e = (int)((bits >> 52) & 0x7ff) - 1023;
     const double mant = __longlong_as_double((bits & 0x000fffffffffffffll) | 0x3ff0000000000000ll);
-    const double t = fma((double)e + (double)__log2f((float)mant), s.ln2_b, -s.lna_b);
-    const double ft = floor(t), fr = t - ft;
-    if (fr > 4e-4 && fr < 1.0 - 4e-4 && s.b >= 1e-3) ir = 1 + (int)ft;
+    const double t = fma((double)e + (double)lg2_approx((float)mant), s.ln2_b, -s.lna_b);
+    const int ti = __double2int_rd(t);
+    const double fr = t - (double)ti;
+    if (fr > 4e-4 && fr < 1.0 - 4e-4) ir = 1 + ti;                     // false for NaN (b < 1e-3)
     else ir = 1 + (int)floor(__ddiv_rn(log(__ddiv_rn(r0, s.a)), s.b));
-    r = r0;
   }
   const int base = min(max(ir, 2), s.n - 2) - 2;                       // :110, 0-based first node of the stencil
   // The 4-node Lagrange interpolant (:112-133) is one cubic per stencil: the host expands it once, in extended precision,
@@ -104,14 +113,15 @@ __device__ __forceinline__ void radial_interp(const PromolDev &m, const SpcDev &
 
 constexpr int PROMOL_PT = 256;    // points per tile = threads per CTA
 constexpr int PROMOL_CAP = 768;   // shared-memory atom list capacity (>= 2*PROMOL_PT)
-constexpr int PROMOL_NSPC = 8;    // species whose constants are staged in shared memory
+constexpr int PROMOL_NSPC = 16;   // species whose constants are staged in shared memory (SPCG = false)
 
-template <int ND>
+// SPCG: more than PROMOL_NSPC species -> their constants are read from global memory (same code otherwise)
+template <int ND, bool SPCG>
 __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel(const __grid_constant__ PromolParams p) {
   constexpr int NT = PROMOL_PT, NW = NT / 32;
   __shared__ double4 s_atom[PROMOL_CAP];
-  __shared__ double s_rc2[PROMOL_CAP];       // squared cutoff of the candidate's species
-  __shared__ SpcDev s_spc[PROMOL_NSPC];      // species constants (global memory beyond PROMOL_NSPC species)
+  __shared__ double s_rc2[PROMOL_CAP];       // squared cutoff of the candidate's species, upper edge of the rounding band
+  __shared__ SpcDev s_spc[SPCG ? 1 : PROMOL_NSPC];   // species constants
   __shared__ int s_cnt[NW], s_rowoff[NT], s_rowi0[NT];
   __shared__ double s_red[NW * 6];
   __shared__ double s_bb[6];
@@ -127,11 +137,8 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
   const bool valid = a < na && b < nb && c < g.c1;
   if (!tile_owned(g, tb0, tc0)) return;      // core pre-pass: another part's unit (block-uniform)
 
-  const SpcDev *spc = m.spc;
-  if (m.nspc <= PROMOL_NSPC) {               // visible after the barriers of the bounding-box reduction below
-    if (tid < m.nspc) s_spc[tid] = m.spc[tid];
-    spc = s_spc;
-  }
+  if (!SPCG && tid < m.nspc) s_spc[tid] = m.spc[tid];   // visible after the barriers of the bounding-box reduction below
+  auto species = [&](int is) -> const SpcDev & { return SPCG ? m.spc[is] : s_spc[is]; };
   double xc[3] = {0, 0, 0};
   double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
   if (valid) {
@@ -188,24 +195,27 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
         const double ex = at.x - xc[0], ey = at.y - xc[1], ez = at.z - xc[2];
         const double d2 = ex * ex + ey * ey + ez * ez;
         isnuc = isnuc || d2 < 1e-10;                                 // src/environmod@proc.f90:677
-        const double rc2 = s_rc2[i];
-        if (d2 > rc2 * (1.0 + 1e-14)) continue;                      // :998, outside for certain
+        const double rc2hi = s_rc2[i];                               // rcut^2 (1 + 1e-14)
+        if (d2 > rc2hi) continue;                                    // :998, outside for certain
         int is, cidx;
         unpack_atom(at, is, cidx);
-        const SpcDev &s = spc[is];
-        if (d2 >= rc2 * (1.0 - 1e-14) && norm2_ref(ex, ey, ez) > s.rcut) continue;   // rounding band: the reference's norm2
+        const SpcDev &s = species(is);
         if (s.n == 0) continue;                                      // :1298-1299
         if (m.fragmask && !m.fragmask[cidx]) continue;               // :1287-1290
-        npair++;
-        // dist (:988, gfortran norm2) = sqrt(d2) to ~2 ulp, which moves rho by ~1e-13 relative; only at the table end,
-        // where interp switches to exactly 0 (:98), is the reference's own scaled arithmetic replayed.  The test
-        // r > cutrad (:1295) cannot fire here: r <= rcut = min(cutrad, rmax).
+        // dist (:988, gfortran norm2) = sqrt(d2) to ~2 ulp, which moves rho by ~1e-13 relative.  Only inside the rounding
+        // band of the cutoff (:998) and at the table end, where interp switches to exactly 0 (:98), is the reference's own
+        // scaled arithmetic replayed.  The test r > cutrad (:1295) cannot fire: r <= rcut = min(cutrad, rmax).
         double r = __dsqrt_rn(d2);
-        if (r > s.rmax * (1.0 - 1e-14)) r = norm2_ref(ex, ey, ez);
-        r = fmax(fmax(r, s.r1), 1e-14);                              // :1302
+        if (d2 >= rc2hi * (1.0 - 2.5e-14) || r > s.rmax_lo) {        // rare: decide with norm2 like the reference
+          r = norm2_ref(ex, ey, ez);
+          if (r > s.rcut) continue;                                  // :998
+          if (r >= s.rmax) { npair++; continue; }                    // :98: inside the cutoff, contributes exactly 0
+        }
+        npair++;
+        r = r < s.rfloor ? s.rfloor : r;                             // :1302
         double rho, rhop, rhopp;
         radial_interp<ND>(m, s, r, rho, rhop, rhopp);
-        rho = fmax(rho, 0.0);                                        // :1304
+        rho = rho < 0.0 ? 0.0 : rho;                                 // :1304
         f += rho;
         if (ND > 1) {
           const double xx = xc[0] - at.x, yy = xc[1] - at.y, zz = xc[2] - at.z;
@@ -272,9 +282,10 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel
         at = m.atoms[s_rowi0[lo_r] + (v - s_rowoff[lo_r])];
         int is, cidx;
         unpack_atom(at, is, cidx);
-        rc2 = spc[is].rcut;
+        rc2 = species(is).rcut;
         rc2 *= rc2;
         act = box_d2(s_bb, at.x, at.y, at.z) <= rc2 * (1.0 + 1e-12) + 1e-9;
+        rc2 *= 1.0 + 1e-14;                 // upper edge of the rounding band of the per-point test
       }
       const unsigned mk = __ballot_sync(~0u, act);
       __syncthreads();                      // s_cnt of the previous pass / the prefix sums has been read by everyone

@@ -5,9 +5,10 @@ namespace c2 {
 
 cudaError_t promol_launch(int nd, const PromolParams &p, int grid, cudaStream_t st) {
   if (grid <= 0) return cudaSuccess;
-  if (nd == 1) promol_grid_kernel<1><<<grid, PROMOL_PT, 0, st>>>(p);
-  else if (nd == 4) promol_grid_kernel<4><<<grid, PROMOL_PT, 0, st>>>(p);
-  else promol_grid_kernel<10><<<grid, PROMOL_PT, 0, st>>>(p);
+  const bool g = p.m.nspc > PROMOL_NSPC;   // species constants from global memory
+  if (nd == 1) { if (g) promol_grid_kernel<1, true><<<grid, PROMOL_PT, 0, st>>>(p); else promol_grid_kernel<1, false><<<grid, PROMOL_PT, 0, st>>>(p); }
+  else if (nd == 4) { if (g) promol_grid_kernel<4, true><<<grid, PROMOL_PT, 0, st>>>(p); else promol_grid_kernel<4, false><<<grid, PROMOL_PT, 0, st>>>(p); }
+  else { if (g) promol_grid_kernel<10, true><<<grid, PROMOL_PT, 0, st>>>(p); else promol_grid_kernel<10, false><<<grid, PROMOL_PT, 0, st>>>(p); }
   g_launches++;
   return cudaGetLastError();
 }
