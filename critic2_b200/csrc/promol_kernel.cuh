@@ -117,7 +117,7 @@ constexpr int PROMOL_NSPC = 16;   // species whose constants are staged in share
 
 // SPCG: more than PROMOL_NSPC species -> their constants are read from global memory (same code otherwise)
 template <int ND, bool SPCG>
-__global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 3 : 2) promol_grid_kernel(const __grid_constant__ PromolParams p) {
+__global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 4 : 3) promol_grid_kernel(const __grid_constant__ PromolParams p) {
   constexpr int NT = PROMOL_PT, NW = NT / 32;
   __shared__ double4 s_atom[PROMOL_CAP];
   __shared__ double s_rc2[PROMOL_CAP];       // squared cutoff of the candidate's species, upper edge of the rounding band
