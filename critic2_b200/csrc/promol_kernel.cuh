@@ -133,7 +133,16 @@ __global__ void __launch_bounds__(PROMOL_PT, ND == 1 ? 4 : 3) promol_grid_kernel
   int ia, ib, ic;
   part_item(g, t, p.nta, p.ntb, ia, ib, ic);
   const int ta0 = ia * g.ta, tb0 = ib * g.tb, tc0 = g.c0 + ic * g.tc;
-  const int a = ta0 + tid % g.ta, b = tb0 + (tid / g.ta) % g.tb, c = tc0 + tid / (g.ta * g.tb);
+  // Lattice tiles (8x8x4): every warp takes a compact 4x4x2 brick so that its 32 points see an atom at nearly the same
+  // distance (lanes share table records: fewer distinct lines per gather, the L1 data stage is the busiest unit);
+  // 4 consecutive points along a = one 32-byte sector per store.  Point lists (ta = 256) stay linear.
+  int a, b, c;
+  if (g.pts) { a = ta0 + tid; b = tb0; c = tc0; }
+  else {
+    a = ta0 + (lane & 3) + 4 * (warp & 1);
+    b = tb0 + ((lane >> 2) & 3) + 4 * ((warp >> 1) & 1);
+    c = tc0 + (lane >> 4) + 2 * (warp >> 2);
+  }
   const bool valid = a < na && b < nb && c < g.c1;
   if (!tile_owned(g, tb0, tc0)) return;      // core pre-pass: another part's unit (block-uniform)
 
