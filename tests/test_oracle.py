@@ -333,3 +333,35 @@ def test_core_augmentation_of_grd_and_grd0():
     # on the nucleus the gradient (valence + core) is nullified (:836-838)
     nuc = aug.grd(st.r[0], 2, True)
     assert nuc[15] == 1.0 and np.all(nuc[1:4] == 0.0) and nuc[0] > plain.grd(st.r[0], 2, True)[0]
+
+
+def test_periodic_promolecular_against_brute_force_lattice_sum():
+    """Pins the crystal side of environ%promolecular (environment images, the region walk of list_near_atoms, y2z_center,
+    environmod@proc.f90:139-213,426-444,895-1047) on alpha-quartz: the oracle against a brute-force sum over lattice
+    translations of the same table interpolation, at points inside and outside the cell, plus lattice periodicity."""
+    st = cases.quartz(1)
+    tabs = cases.tables()
+    grids = oracle.Grid1Set(tabs)
+    fld = oracle.Field(oracle.Environ(st), grids=grids)
+    rng = np.random.default_rng(11)
+    frac = rng.uniform(-1.3, 2.1, (25, 3))
+    pts = frac @ st.m_x2c.T
+    res = fld.grd_points(pts, 2, True)
+    from critic2_b200.structure import CUTRAD
+    nmax = 6
+    shifts = np.array([[i, j, k] for i in range(-nmax, nmax + 1) for j in range(-nmax, nmax + 1)
+                       for k in range(-nmax, nmax + 1)], float) @ st.m_x2c.T
+    for p, rr in zip(pts, res):
+        rho, grad = 0.0, np.zeros(3)
+        for xat, zat in zip(st.r, st.z):
+            rc = min(CUTRAD[int(zat) - 1], tabs[int(zat)]["r"][-1])
+            d = p[None, :] - (xat[None, :] + shifts)
+            dist = np.linalg.norm(d, axis=1)
+            for k in np.nonzero(dist <= rc)[0]:
+                f0, fp0, _ = grids.interp(int(zat), max(float(dist[k]), float(tabs[int(zat)]["r"][0])))
+                rho += max(f0, 0.0)
+                grad += d[k] / dist[k] * fp0
+        assert abs(rr[0] - rho) <= 1e-12 * rho
+        np.testing.assert_allclose(rr[1:4], grad, rtol=0, atol=1e-11 * max(1.0, np.abs(grad).max()))
+    moved = fld.grd_points(pts + (np.array([1.0, -2.0, 1.0]) @ st.m_x2c.T), 2, True)
+    np.testing.assert_allclose(moved[:, :13], res[:, :13], rtol=1e-10, atol=1e-13)
