@@ -546,3 +546,32 @@ def test_core_on_a_promolecular_crystal_field(G, O):
     o, xd, nn = drivers.cube_grid(st, (18, 17, 20))
     ref = of.cube(o, xd, nn, periodic=True)
     _compare_cube(fld.cube(o, xd, nn, periodic=True), ref)
+
+
+def test_promolecular_many_species_and_table_edges(G, O):
+    """More species than the kernel stages in shared memory (constants then come from global memory), elements without a
+    table (agrid not initialised: skipped, environmod@proc.f90:1298-1299), and points on the table edges: exactly on a
+    nucleus (r clamped to r(1), :1302), at the last node and just past it (interp returns 0 from rmax on, grid1mod :98)."""
+    from critic2_b200 import structure
+    rng = np.random.default_rng(21)
+    zs = np.array([1, 6, 7, 8, 14, 2, 3, 4, 5, 9, 10, 11, 12, 13, 15, 16, 17, 18, 19, 20], np.int32)   # 20 species
+    xyz = rng.uniform(0.0, 9.0, (len(zs), 3))
+    st = structure.molecular_cell(xyz, zs)
+    tabs = cases.tables()
+    fld = G.PromolField(st, tabs)
+    of = O.Field(O.Environ(st), grids=O.Grid1Set(tabs))
+    x0, xd, nn = cases.bbox_grid(st, (19, 17, 15), margin=3.0)
+    _compare_cube(fld.cube(x0, xd, nn), of.cube(x0, xd, nn))
+    # table edges of the oxygen atom (index 3), approached along x where no other tabulated atom is within reach
+    far = structure.molecular_cell(np.array([[0.0, 0.0, 0.0], [40.0, 0.0, 0.0]]), np.array([8, 1], np.int32))
+    fldf = G.PromolField(far, tabs)
+    off = O.Field(O.Environ(far), grids=O.Grid1Set(tabs))
+    rmax, r1 = float(tabs[8]["r"][-1]), float(tabs[8]["r"][0])
+    d = np.array([0.0, 0.5 * r1, r1, float(tabs[8]["r"][1]), float(tabs[8]["r"][-2]), rmax * (1 - 1e-15), rmax,
+                  rmax * (1 + 1e-15), rmax + 1e-9])
+    pts = far.r[0] + np.outer(d, [-1.0, 0.0, 0.0])
+    res, rres = fldf.points(pts, 2, True), off.grd_points(pts, 2, True)
+    assert np.array_equal(res[:, 0] == 0.0, rres[:, 0] == 0.0) and rres[-3:, 0].max() == 0.0 and rres[0, 15] == 1.0
+    check_rho(res[:, 0], rres[:, 0])
+    check_vec(res[:, 1:4], rres[:, 1:4], "grad", rho=rres[:, 0])
+    check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])
