@@ -84,6 +84,19 @@ __device__ __forceinline__ void prim_chi(double x, double y, double z, int lx, i
   }
 }
 
+// prim_chi with WfnParams::chi_mode: in value-only launches bits 0-1 select a Cartesian derivative as the "value"
+template <int ND>
+__device__ __forceinline__ void prim_chi_mode(double x, double y, double z, int lx, int ly, int lz, double al, double ex,
+                                              int mode, double *chi) {
+  if (ND == 1 && (mode & 3)) {
+    double c[4];
+    prim_chi<4>(x, y, z, lx, ly, lz, al, ex, c);
+    const int k = mode & 3;
+    chi[0] = k == 1 ? c[1] : (k == 2 ? c[2] : c[3]);
+  } else
+    prim_chi<ND>(x, y, z, lx, ly, lz, al, ex, chi);
+}
+
 // ---- PTX wrappers: mbarrier + 1-D bulk TMA copy + FP64 tensor-core MMA -------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 

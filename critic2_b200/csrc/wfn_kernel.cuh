@@ -37,6 +37,11 @@ struct WfnParams {
   int *acache_nz;       // [grid][2][acache_chunks][8] k-quad masks
   double *ws_rec;       // [grid][prim_cap][8] records of the active primitives of the current sub-tile
   int acache_chunks;
+  // value-only (ND = 1) launches only.  bits 0-1 = k in 1..3: the basis value is replaced by its k-th Cartesian derivative,
+  // so the pass returns sum_mo occ (d_k phi)^2 -- three such passes give the kinetic energy density G = res%gkin
+  // (rho2, src/wfn_private@proc.F90:2104-2106,2209).  bit 2 (block-synchronous kernels): the MO sum is linear, sum_mo
+  // occ phi -- with a one-MO handle that is the MO value of calculate_mo (:2447-2553).
+  int chi_mode;
 };
 
 // NFRAG = 8-column MMA fragments per MO block, dealt to the WN warp columns: warp column wn owns
@@ -268,7 +273,7 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
             if (within_cut(dx, dy, dz, d2, cut.x, cut.y)) {          // :2747
               const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[prim];
               const double ex = exp(-xa.w * d2);                      // :2749
-              prim_chi<ND>(dx, dy, dz, l.x, l.y, l.z, xa.w, ex, chi);
+              prim_chi_mode<ND>(dx, dy, dz, l.x, l.y, l.z, xa.w, ex, p.chi_mode, chi);
               nz = true;
             }
           }
@@ -335,7 +340,7 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
             for (int j = 0; j < 2; j++) {
               const double oc = (NFRAG % WN == 0 || ni < nfw) ? w.occ[blk * NB + (f0 + ni) * 8 + 2 * (lane & 3) + j] : 0.0;
               const double f0v = acc[0][ni][j];
-              q[0] += oc * f0v * f0v;
+              q[0] += (ND == 1 && (p.chi_mode & 4)) ? oc * f0v : oc * f0v * f0v;
               if (ND > 1) {
                 const double t = 2.0 * oc;
                 const double f1 = acc[ND > 1 ? 1 : 0][ni][j], f2 = acc[ND > 1 ? 2 : 0][ni][j], f3 = acc[ND > 1 ? 3 : 0][ni][j];

@@ -308,8 +308,8 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
               ex = pass ? exp(-al * d2) : 0.0;
             }
             if (pass) {
-              prim_chi<ND>(dx, dy, dz, (int)((bits >> 32) & 0xff), (int)((bits >> 40) & 0xff), (int)((bits >> 48) & 0xff),
-                           al, ex, chi);
+              prim_chi_mode<ND>(dx, dy, dz, (int)((bits >> 32) & 0xff), (int)((bits >> 40) & 0xff),
+                                (int)((bits >> 48) & 0xff), al, ex, p.chi_mode, chi);
               nzbits |= 1u;
             }
           }

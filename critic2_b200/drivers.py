@@ -312,10 +312,25 @@ def rhoplot_plane(field: "gpu._Field", st: Structure, x0, x1, x2, nx: int, ny: i
 
 
 def mesh_fill(field: "gpu._Field", pts, props=("rho",), periodic: bool = True):
-    """mesh%fill (meshmod@proc.f90:446-470) for the properties the path provides: 'volume' (1), 'rho' (res%f),
-    'gradrho' (res%gfmod).  pts (n,3) Cartesian mesh nodes; returns f (n, len(props))."""
-    nder = max([-1] + [{"volume": -1, "rho": 0, "gradrho": 1}[p] for p in props])
+    """mesh%fill (meshmod@proc.f90:420-470).  props: 'volume' (1), 'rho' (res%f), 'gradrho' (res%gfmod), 'gkin' (res%gkin,
+    wavefunction fields) or an integer > 100 = MO number prop - 100 (res%fspc of grd(nder=-1), wavefunction fields).
+    pts (n,3) Cartesian mesh nodes; returns f (n, len(props))."""
+    nders = {"volume": -1, "rho": 0, "gradrho": 1, "gkin": -1}
+    nder = max([-1] + [nders[p] for p in props if not isinstance(p, int)])
     pts = np.asarray(pts, float).reshape(-1, 3)
     res = field.points(pts, nder=nder, periodic=periodic) if nder >= 0 else None
-    cols = {"volume": lambda: np.ones(pts.shape[0]), "rho": lambda: res[:, 0], "gradrho": lambda: res[:, 13]}
-    return np.stack([cols[p]() for p in props], axis=1)
+    cols = []
+    for p in props:
+        if isinstance(p, int):
+            if p <= 100:
+                raise ValueError("MO properties are 100 + n")
+            cols.append(field.mo_points(pts, p - 100, periodic))
+        elif p == "volume":
+            cols.append(np.ones(pts.shape[0]))
+        elif p == "rho":
+            cols.append(res[:, 0])
+        elif p == "gradrho":
+            cols.append(res[:, 13])
+        else:
+            cols.append(field.gkin_points(pts, periodic))
+    return np.stack(cols, axis=1)

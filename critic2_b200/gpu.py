@@ -89,6 +89,8 @@ def lib():
         L.c2gpu_promol_grid.argtypes = [C.c_void_p, ip, dp]
         L.c2gpu_promol_grid_dev.argtypes = [C.c_void_p, ip, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_eval_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp]
+        L.c2gpu_eval_points_gkin.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, dp]
+        L.c2gpu_eval_points_mo.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, dp]
         L.c2gpu_wfn_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_int, dp]
         L.c2gpu_promol_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, dp]
         L.c2gpu_wfn_config.argtypes = [C.c_void_p, ip]
@@ -269,6 +271,24 @@ class WfnField(_Field):
             C.byref(h)))
         self.handle = h
 
+    # -- res%gkin of grd (rho2, wfn_private@proc.F90:2104-2106,2209): mesh%fill's im_gkin ----------------------------
+    def gkin_points(self, pts, periodic: bool = True):
+        pts = _f64(pts).reshape(-1, 3)
+        out = np.empty(pts.shape[0])
+        _check(lib().c2gpu_eval_points_gkin(self.handle, pts.shape[0], _d(pts), int(periodic), _d(out)))
+        return out
+
+    # -- grd(nder=-1, fder) -> calculate_mo (wfn_private@proc.F90:2447-2553): mesh%fill's prop > 100 --------------------
+    def mo_field(self, imo: int) -> "MoField":
+        """One-MO companion handle for MO number imo (1-based, <= nmoall); cached per MO."""
+        cache = self.__dict__.setdefault("_mo", {})
+        if imo not in cache:
+            cache[imo] = MoField(self.f, self.st, imo)
+        return cache[imo]
+
+    def mo_points(self, pts, imo: int, periodic: bool = True):
+        return self.mo_field(imo).values(pts, periodic)
+
     def config(self):
         a = np.zeros(8, np.int32)
         _check(lib().c2gpu_wfn_config(self.handle, _i(a)))
@@ -281,6 +301,29 @@ class WfnField(_Field):
         _check(lib().c2gpu_wfn_count_active(self.handle, _d(x0a), _d(xda), _i(nna), int(periodic), iz0,
                                             int(nna[2]) if iz1 is None else iz1, C.byref(s)))
         return s.value
+
+
+class MoField(_Field):
+    """The one-MO wavefunction handle c2gpu_eval_points_mo evaluates: same primitives, cmo = row imo (1-based)."""
+
+    def __init__(self, f, st, imo: int):
+        if not 1 <= imo <= f.cmo.shape[1]:
+            raise C2GpuError("Invalid molecular orbital")        # calculate_mo :2531-2532
+        h = C.c_void_p()
+        row = np.ascontiguousarray(f.cmo[:, imo - 1])
+        one = np.ones(1)
+        _check(lib().c2gpu_wfn_create(
+            f.natom, _d(_f64(st.r)), f.npri, _i(_i32(f.icenter)), _i(_i32(f.itype)), _d(_f64(f.e)), _d(_f64(f.dran)),
+            1, 1, _d(row), _d(one), 0, 1, 0, None, None, None, None, None, int(st.ismolecule), _d(_colmajor(st.m_x2c)),
+            _d(_colmajor(st.m_c2x)), C.byref(h)))
+        self.handle = h
+        self.imo = imo
+
+    def values(self, pts, periodic: bool = True):
+        pts = _f64(pts).reshape(-1, 3)
+        out = np.empty(pts.shape[0])
+        _check(lib().c2gpu_eval_points_mo(self.handle, pts.shape[0], _d(pts), int(periodic), _d(out)))
+        return out
 
 
 class PromolField(_Field):

@@ -17,7 +17,7 @@ module gpu_interface
 
   public :: gpu_enabled, gpu_init, gpu_end
   public :: gpu_wfn_handle, gpu_promol_handle, gpu_set_core, gpu_destroy
-  public :: gpu_cube, gpu_nciplot, gpu_nci_cutoffs, gpu_promolecular_grid
+  public :: gpu_cube, gpu_nciplot, gpu_nci_cutoffs, gpu_promolecular_grid, gpu_fillmesh, gpu_fillmesh_mo
 
   logical, save :: gpu_enabled = .false. !< set by the GPU keyword (global@proc.f90, critic_setvariables)
 
@@ -142,6 +142,33 @@ module gpu_interface
        character(kind=c_char) :: text(*)
        integer(c_int) :: ierr
      end function c2gpu_dat_text
+     function c2gpu_eval_points(h,npts,pts,nder,periodic,res) bind(c,name="c2gpu_eval_points") result(ierr)
+       import :: c_int, c_long, c_double, c_ptr
+       type(c_ptr), value :: h
+       integer(c_long), value :: npts
+       real(c_double), intent(in) :: pts(3,*)
+       integer(c_int), value :: nder, periodic
+       real(c_double), intent(inout) :: res(16,*)
+       integer(c_int) :: ierr
+     end function c2gpu_eval_points
+     function c2gpu_eval_points_gkin(h,npts,pts,periodic,gkin) bind(c,name="c2gpu_eval_points_gkin") result(ierr)
+       import :: c_int, c_long, c_double, c_ptr
+       type(c_ptr), value :: h
+       integer(c_long), value :: npts
+       real(c_double), intent(in) :: pts(3,*)
+       integer(c_int), value :: periodic
+       real(c_double), intent(inout) :: gkin(*)
+       integer(c_int) :: ierr
+     end function c2gpu_eval_points_gkin
+     function c2gpu_eval_points_mo(hmo,npts,pts,periodic,phi) bind(c,name="c2gpu_eval_points_mo") result(ierr)
+       import :: c_int, c_long, c_double, c_ptr
+       type(c_ptr), value :: hmo
+       integer(c_long), value :: npts
+       real(c_double), intent(in) :: pts(3,*)
+       integer(c_int), value :: periodic
+       real(c_double), intent(inout) :: phi(*)
+       integer(c_int) :: ierr
+     end function c2gpu_eval_points_mo
      function c2gpu_promol_grid(h,n,out) bind(c,name="c2gpu_promol_grid") result(ierr)
        import :: c_int, c_double, c_ptr
        type(c_ptr), value :: h
@@ -188,12 +215,17 @@ contains
 
   !> Device image of a wavefunction field (called from field_new after complete_struct; freed in field_end).
   !> Returns c_null_ptr when the input is unsupported (STO basis, crystal environment): the caller keeps grd.
-  function gpu_wfn_handle(w,c) result(h)
+  !> With imo the handle holds that molecular orbital alone (nmoocc = 1, cmo = cmo(imo,:), occ = 1): the operand of
+  !> c2gpu_eval_points_mo (calculate_mo, wfn_private@proc.F90:2447-2553; imo may address a virtual orbital).
+  function gpu_wfn_handle(w,c,imo) result(h)
     use wfn_private, only: molwfn, wfn_frac
     use crystalmod, only: crystal
     type(molwfn), intent(in), target :: w
     type(crystal), intent(in) :: c
+    integer, intent(in), optional :: imo
     type(c_ptr) :: h
+    real(c_double), allocatable :: row(:)
+    real(c_double) :: one(1)
     real(c_double), allocatable :: xyz(:,:)
     integer(c_int) :: ierr, ldc
     integer :: i
@@ -206,7 +238,14 @@ contains
        xyz(:,i) = w%env%at(i)%r
     end do
     ldc = size(w%cmo,1)
-    if (w%nedf > 0) then
+    if (present(imo)) then
+       if (imo < 1 .or. imo > ldc) return
+       allocate(row(w%npri))
+       row = w%cmo(imo,:)
+       one = 1d0
+       ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
+          1_c_int,1_c_int,row,one,0_c_int,1_c_int,0_c_int,dumi,dumi,dumr,dumr,dumr,1_c_int,c%m_x2c,c%m_c2x,h)
+    else if (w%nedf > 0) then
        ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
           int(w%nmoocc,c_int),ldc,w%cmo,w%occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),int(w%nedf,c_int),&
           w%icenter_edf,w%itype_edf,w%e_edf,w%c_edf,w%dran_edf,1_c_int,c%m_x2c,c%m_c2x,h)
@@ -523,5 +562,50 @@ contains
     call gpu_check("promolecular_grid",ierr)
     ok = (ierr == 0)
   end subroutine gpu_promolecular_grid
+
+  !> mesh%fill (meshmod@proc.f90:446-470) on the GPU for im_rho / im_gradrho / im_gkin: one call per property column.
+  !> iprop: 0 rho (res%f), 1 gradrho (res%gfmod), 2 gkin (res%gkin; wavefunction fields only).
+  subroutine gpu_fillmesh(h,x,iprop,periodic,fcol,ok)
+    type(c_ptr), intent(in) :: h
+    real*8, intent(in) :: x(:,:)          !< m%x(3,n)
+    integer, intent(in) :: iprop
+    logical, intent(in) :: periodic
+    real*8, intent(inout) :: fcol(:)      !< m%f(:,j)
+    logical, intent(out) :: ok
+    real(c_double), allocatable :: res(:,:)
+    integer(c_int) :: ierr, iper
+    integer(c_long) :: n
+    ok = .false.
+    if (.not.c_associated(h)) return
+    n = size(x,2)
+    iper = merge(1_c_int,0_c_int,periodic)
+    if (iprop == 2) then
+       ierr = c2gpu_eval_points_gkin(h,n,x,iper,fcol)
+    else
+       allocate(res(16,n))
+       ierr = c2gpu_eval_points(h,n,x,int(iprop,c_int),iper,res)
+       if (ierr == 0) fcol = res(merge(1,14,iprop==0),:)      ! res%f, res%gfmod
+    end if
+    if (ierr == -1) return
+    call gpu_check("gpu_fillmesh",ierr)
+    ok = .true.
+  end subroutine gpu_fillmesh
+
+  !> mesh%fill with prop > 100 (MO values, grd nder=-1 -> calculate_mo): hmo is the one-MO handle made by
+  !> gpu_wfn_handle over the row cmo(imo,:) (see INTEGRATION.md).
+  subroutine gpu_fillmesh_mo(hmo,x,periodic,fcol,ok)
+    type(c_ptr), intent(in) :: hmo
+    real*8, intent(in) :: x(:,:)
+    logical, intent(in) :: periodic
+    real*8, intent(inout) :: fcol(:)
+    logical, intent(out) :: ok
+    integer(c_int) :: ierr
+    ok = .false.
+    if (.not.c_associated(hmo)) return
+    ierr = c2gpu_eval_points_mo(hmo,int(size(x,2),c_long),x,merge(1_c_int,0_c_int,periodic),fcol)
+    if (ierr == -1) return
+    call gpu_check("gpu_fillmesh_mo",ierr)
+    ok = .true.
+  end subroutine gpu_fillmesh_mo
 
 end module gpu_interface

@@ -179,6 +179,17 @@ int c2gpu_promol_grid_dev(void *hpromol, const int n[3], double *out_dev, int iz
 #define C2GPU_RES_LEN 16
 int c2gpu_eval_points(void *h, long npts, const double *pts, int nder, int periodic, double *res);
 
+/* Kinetic energy density G(r) = res%gkin of grd (nder >= 1) for wavefunction fields: 1/2 sum_mo occ |grad phi_mo|^2
+   (rho2, src/wfn_private@proc.F90:2104-2106,2209; src/fieldmod@proc.f90:776) -- mesh%fill's im_gkin
+   (src/meshmod@proc.f90:436-437,459-460).  Three value-only passes with the basis value replaced by its x, y, z derivative.
+   gkin: npts doubles.  Promolecular handles return -1 (the reference has no gkin for them: avail_gkin stays false). */
+int c2gpu_eval_points_gkin(void *h, long npts, const double *pts, int periodic, double *gkin);
+/* MO values: grd(nder = -1, fder) -> calculate_mo (src/wfn_private@proc.F90:2447-2553), mesh%fill's prop > 100
+   (src/meshmod@proc.f90:461-464): phi(x) = sum_p cmo(imo,p) chi_p(x) over the primitives inside their dran.
+   h_mo is a wavefunction handle made by c2gpu_wfn_create over the same primitives with nmoocc = 1, ldc = 1 and
+   cmo = the row cmo(imo,:) (the caller resolves fder -> imo as :2461-2530 do), occ = 1.  phi: npts doubles. */
+int c2gpu_eval_points_mo(void *h_mo, long npts, const double *pts, int periodic, double *phi);
+
 /* ---- diagnostics used by the roofline accounting -------------------------------------------- */
 /* Sum over the grid slab of n_act(p) = #{primitives with dist <= dran} (the reference's own screen, :2747). */
 int c2gpu_wfn_count_active(void *h, const double x0[3], const double xd[9], const int nn[3], int periodic, int iz0,

@@ -72,6 +72,7 @@ def lib():
         L.orc_cube_text.argtypes = [dp, ip, C.c_int, C.c_int, C.c_char_p, C.c_int]
         L.orc_promolecular_grid.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), ip, dp, C.c_int]
         L.orc_grd_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
+        L.orc_mo_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
         L.orc_nact_points.argtypes = [C.c_void_p, C.c_void_p, C.c_long, dp, C.POINTER(C.c_long), C.c_int]
         L.orc_cutrad.restype = C.c_double
         L.orc_cutrad.argtypes = [C.c_int]
@@ -221,6 +222,13 @@ class Field:
         res = np.zeros((pts.shape[0], RES_LEN))
         lib().orc_grd_points(self.ref, pts.shape[0], _d(pts), nder, int(periodic), _d(res), nthreads)
         return res
+
+    def mo_points(self, pts, imo: int, periodic=True, nthreads=0):
+        """grd(nder=-1, fder=imo): MO values (imo 1-based)"""
+        pts = _f64(pts)
+        out = np.zeros(pts.shape[0])
+        lib().orc_mo_points(self.ref, pts.shape[0], _d(pts), int(imo), int(periodic), _d(out), nthreads)
+        return out
 
     def nact_points(self, pts, nthreads=0):
         pts = _f64(pts)

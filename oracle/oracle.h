@@ -79,6 +79,8 @@ void orc_wfn_tables(const orc_wfn *f, double *dran, double *spcutoff, int *lmax,
 /* rho2: out[0..2]=rho(3) [3..5]=rhoval(3) [6..14]=grad(3,3) [15..23]=gradval(3,3) [24..50]=h(3,3,3)
    [51..77]=hval [78..80]=gkin(3) [81]=vir [82..90]=stress(3,3); all Fortran order. */
 void orc_rho2(const orc_wfn *f, const orc_environ *env, const double *xpos, int nder, double *out91);
+/* calculate_mo (:2447-2553) with a numeric MO selector (1-based, <= nmoall): the MO value at xpos */
+double orc_calculate_mo(const orc_wfn *f, const orc_environ *env, const double *xpos, int imo);
 /* number of primitives passing the reference's own per-point screen (:2747) -- the n_act of SURVEY §8(d) */
 long orc_nact(const orc_wfn *f, const orc_environ *env, const double *xpos);
 
@@ -151,6 +153,8 @@ long orc_text_record_bytes(int nval, int fmt);
 void orc_cube_text(const double *g, const int *n, int fmt, int order, char *text, int nthreads);
 /* evaluate grd on an arbitrary list of points: res is npts*ORC_RES_LEN */
 void orc_grd_points(const orc_field *f, long npts, const double *pts, int nder, int periodic, double *res, int nthreads);
+/* grd(v, nder=-1, fder=imo) on a point list (src/fieldmod@proc.f90:791-793): wrap like grd, then calculate_mo at wcr */
+void orc_mo_points(const orc_field *f, long npts, const double *pts, int imo, int periodic, double *phi, int nthreads);
 void orc_nact_points(const orc_wfn *f, const orc_environ *env, long npts, const double *pts, long *nact, int nthreads);
 
 double orc_cutrad(int z);

@@ -411,6 +411,18 @@ void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const 
       }
 }
 
+void orc_mo_points(const orc_field *f, long npts, const double *pts, int imo, int periodic, double *phi, int nthreads) {
+#ifdef _OPENMP
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic, 64)
+  for (long p = 0; p < npts; p++) {
+    double wc[3], wcr[3];
+    grd_points(f->env, pts + 3 * p, periodic, wc, wcr);
+    phi[p] = orc_calculate_mo(f->wfn, f->env, wcr, imo);
+  }
+}
+
 void orc_grd_points(const orc_field *f, long npts, const double *pts, int nder, int periodic, double *res, int nthreads) {
 #ifdef _OPENMP
   if (nthreads > 0) omp_set_num_threads(nthreads);

@@ -240,6 +240,37 @@ static void calculate_edf(const orc_wfn *f, const orc_environ *env, const double
   }
 }
 
+/* calculate_mo :2447-2553 for a numeric selector: phi_imo(xpos) through calculate_mo_gto(imo,imo,imo,nder=0); imo is
+   1-based and may address a virtual orbital (<= nmoall) */
+double orc_calculate_mo(const orc_wfn *f, const orc_environ *env, const double *xpos, int imo) {
+  double phi = 0.0;
+  if (imo < 1 || imo > f->nmoall) return 0.0 / 0.0;             /* :2531-2532 is a fatal error in the reference */
+  int *eid = malloc(sizeof(int) * env->n);
+  double *dist = malloc(sizeof(double) * env->n);
+  int nenv, lvec[3];
+  int ierr = orc_list_near_atoms(env, xpos, 0, f->spcutoff, &nenv, eid, dist, lvec); /* :2535 */
+  if (!ierr) {
+    double xl[3][3][6];
+    for (int i = 0; i < nenv; i++) {
+      int iat = env->cidx[eid[i]];
+      double d2 = dist[i] * dist[i];
+      const double *ra = env->r + 3 * (iat - 1);
+      double xx[3] = {xpos[0] - ra[0], xpos[1] - ra[1], xpos[2] - ra[2]};
+      powers(xx, f->lmax[iat - 1], xl);
+      for (int j = f->iprilo[iat - 1]; j <= f->iprihi[iat - 1]; j++) {
+        int ipri = f->icord[j - 1] - 1;
+        if (dist[i] > f->dran[ipri]) continue;                  /* :2747 */
+        double al = f->e[ipri], chi[10];
+        prim_chi(xx, xl, li[f->itype[ipri] - 1], al, exp(-al * d2), 0, chi);
+        phi += f->cmo[(size_t)ipri * f->nmoall + (imo - 1)] * chi[0];
+      }
+    }
+  }
+  free(eid);
+  free(dist);
+  return phi;
+}
+
 long orc_nact(const orc_wfn *f, const orc_environ *env, const double *xpos) {
   int *eid = malloc(sizeof(int) * env->n);
   double *dist = malloc(sizeof(double) * env->n);

@@ -575,3 +575,37 @@ def test_promolecular_many_species_and_table_edges(G, O):
     check_rho(res[:, 0], rres[:, 0])
     check_vec(res[:, 1:4], rres[:, 1:4], "grad", rho=rres[:, 0])
     check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])
+
+
+@pytest.mark.parametrize("name,cfg", [("benzene-adz", -1), ("hooh-atz", -1), ("synth", 3), ("synth", 6)])
+def test_gkin_and_mo_values_on_point_lists(G, O, name, cfg):
+    """mesh%fill's remaining properties (meshmod@proc.f90:456-464): res%gkin (three derivative-selected value passes of the
+    wavefunction kernels) and MO values (grd nder=-1 -> calculate_mo, a linear pass over a one-MO handle)."""
+    from critic2_b200 import drivers, synth
+    f = synth.small_synthetic(uhf=True, with_edf=True) if name == "synth" else cases.golden_wfn(name)
+    st = cases.mol_structure(f)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    of = _ofield(O, f, st)
+    rng = np.random.default_rng(13)
+    pts = np.concatenate([st.r[rng.integers(0, f.natom, 700)] + rng.normal(0, 1.5, (700, 3)),
+                          st.r[:2], st.r[0] + np.array([[80.0, 0.0, 0.0]])])        # 703 points: ragged, nuclei, a far point (wrapped)
+    rres = of.grd_points(pts, 1, True)
+    gk = fld.gkin_points(pts)
+    assert np.array_equal(gk == 0.0, rres[:, 17] == 0.0)
+    err = np.abs(gk - rres[:, 17]) / np.maximum(rres[:, 17], 1e-30)
+    assert err.max() <= cases.TOL_DER, f"gkin {err.max():.3e}"
+    for imo in (1, f.nmoocc, min(f.cmo.shape[1], f.nmoocc + 1)):
+        ref = of.mo_points(pts, imo, True)
+        got = fld.mo_points(pts, imo)
+        # an MO can vanish by symmetry (a pi orbital at in-plane points): there both sides hold rounding noise of their own
+        # summation order, so exact zeros are only required where the reference has them (outside every cutoff)
+        assert not got[ref == 0.0].any()
+        assert np.max(np.abs(got - ref)) <= cases.TOL_RHO * np.abs(ref).max(), f"MO {imo}"
+    out = drivers.mesh_fill(fld, pts, props=("volume", "rho", "gradrho", "gkin", 101))
+    assert np.array_equal(out[:, 0], np.ones(len(pts))) and np.array_equal(out[:, 3], gk)
+    check_rho(out[:, 1], rres[:, 0])
+    assert np.array_equal(out[:, 4], fld.mo_points(pts, 1))

@@ -365,3 +365,38 @@ def test_periodic_promolecular_against_brute_force_lattice_sum():
         np.testing.assert_allclose(rr[1:4], grad, rtol=0, atol=1e-11 * max(1.0, np.abs(grad).max()))
     moved = fld.grd_points(pts + (np.array([1.0, -2.0, 1.0]) @ st.m_x2c.T), 2, True)
     np.testing.assert_allclose(moved[:, :13], res[:, :13], rtol=1e-10, atol=1e-13)
+
+
+def dense_phi(f, r_atoms, pts):
+    """MO values (npts, nmoocc) by brute force (no screening) in numpy."""
+    d = pts[:, None, :] - r_atoms[f.icenter - 1][None, :, :]
+    chi = np.prod(d ** LI[f.itype - 1][None, :, :], axis=-1) * np.exp(-f.e[None, :] * (d ** 2).sum(-1))
+    return chi @ f.cmo[:, :f.nmoocc]
+
+
+def test_mo_values_and_gkin_against_dense_numpy():
+    """calculate_mo (wfn_private@proc.F90:2447-2553) and res%gkin = 1/2 sum occ |grad phi|^2 (:2104-2106,2209) against an
+    unscreened numpy evaluation (MO values) and its central differences (gkin)."""
+    f = cases.golden_wfn("hooh-atz")
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    rng = np.random.default_rng(9)
+    pts = st.r[rng.integers(0, f.natom, 60)] + rng.normal(0, 1.0, (60, 3))
+    phi = dense_phi(f, st.r, pts)
+    scale = np.abs(phi).max()
+    for imo in (1, 4, f.nmoocc):
+        got = fld.mo_points(pts, imo, periodic=False)
+        assert np.max(np.abs(got - phi[:, imo - 1])) < 1e-9 * scale
+    h = 1e-4
+    g2 = np.zeros((len(pts), f.nmoocc))
+    for ax in range(3):
+        e = np.zeros(3)
+        e[ax] = h
+        d1 = (8 * (dense_phi(f, st.r, pts + e) - dense_phi(f, st.r, pts - e))
+              - (dense_phi(f, st.r, pts + 2 * e) - dense_phi(f, st.r, pts - 2 * e))) / (12 * h)
+        g2 += d1 ** 2
+    gk = 0.5 * g2 @ f.occ
+    res = fld.grd_points(pts, nder=1, periodic=False)
+    assert np.max(np.abs(res[:, 17] - gk) / gk) < 1e-7
+    far = st.r[0] + np.array([[60.0, 0.0, 0.0]])
+    assert fld.mo_points(far, 1, periodic=False)[0] == 0.0
