@@ -38,6 +38,7 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 if world > 1:
     os.environ["NCCL_DEBUG"] = "WARN"
+    os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"   # the version banner is part of the log: keep stdout for the JSON line
     dist.init_process_group("nccl", device_id=dev)
 gpu.init_devices([local])
 
