@@ -14,11 +14,16 @@ long g_launches = 0;
   X(3, "L", 2, 7, 14, 28, 1)  \
   X(4, "L1", 1, 7, 14, 28, 2) \
   X(5, "L16", 2, 8, 14, 32, 1)
+// M2 = M with two CTAs per SM (128 registers, a few spills): while one CTA sits in the latency-bound chi phase or at its
+// chunk barrier the other one feeds the DMMA pipe.  60-atom molecule, 160^3: 57.3 ms per 64-column block against 72.7 ms
+// for M (48 MOs: 37 -> 47 % of the DMMA peak; 64: 48 -> 62 %; 128: 49 -> 62 %).  Three CTAs (85 registers) or eight warp
+// columns of one fragment (64 registers) spill heavily and are 1.6-3x slower.
 // id after the warp-specialised kernel (id 6): 9..24 MOs with the 24 columns spread over three warp columns, so a thread
 // holds 20 accumulators instead of 60 and two CTAs (24 warps) are resident per SM instead of one (8 warps); measured on
 // benzene NCIPLOT 200^3: 20.9 ms against 22.0 ms for S3 (P = 64 and P = 16 variants of the same idea were slower)
 #define C2_WFN_CONFIGS2(X) \
-  X(7, "S3w", 4, 3, 3, 12, 2)
+  X(7, "S3w", 4, 3, 3, 12, 2) \
+  X(8, "M2", 2, 4, 8, 16, 2)
 
 static void tile_shape(int P, int &ta, int &tb, int &tc) {
   switch (P) {
@@ -80,12 +85,17 @@ int wfn_choose_config(int nmo, int force) {
   int nfrag = (nmo + 7) / 8;
   if (nfrag <= 1) return 0;
   if (nfrag <= 3) return 7;
-  int padM = ((nmo + 63) / 64) * 64, padL = ((nmo + 111) / 112) * 112;
-  if (padM < padL) return 2;
-  // The warp-specialised kernel amortises its chi-tile cache over the MO blocks: measured on a 60-atom molecule it only
-  // ties the block-synchronous L at 2 blocks (nmo = 200: 200.6 vs 196.9 ms) and loses at 1 block; at 7 blocks (cfg 4) it
-  // wins 88 % to 62 %.  A 64-column variant of it (WsCfg<ND, 8>) measured no better than M/L for 48-200 MOs.
-  return nmo > 2 * 112 ? 6 : 3;
+  // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms): M2 54 per 64-column block, L 97 per 112-column
+  // block, the warp-specialised kernel 96 + 52 per 112-column block (its generators run ahead and the chi tiles are
+  // re-used from the L2 cache, which only pays from three blocks up).  tools/probe_mid.py reproduces the table:
+  //   nmo     48    100   128   150   192   224   | 780 (cfg 4, 500 atoms): WS 88 % of the DMMA peak, L 62 %
+  //   M2      57    111   111   164   164   217
+  //   L      103    103   197   197   197   197
+  //   WS     148    148   200   200   200   200
+  const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
+  const int tM = 54 * bM + 3, tL = 97 * bL + 6, tW = 96 + 52 * bL;
+  if (tM <= tL && tM <= tW) return 8;
+  return tL <= tW ? 3 : 6;
 }
 
 template <class C>

@@ -72,7 +72,7 @@ def test_cube_cell_grid_ragged(G, O):
     assert (ref["f"] == 0).any()
 
 
-@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_all_configs(G, O, cfg, variant):
     """24-atom def2-TZVP-shaped synthetic molecule through the M / L / L1 tensor-core tile configurations."""
