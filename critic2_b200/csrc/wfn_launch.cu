@@ -20,7 +20,8 @@ long g_launches = 0;
 // columns of one fragment (64 registers) spill heavily and are 1.6-3x slower.
 // id after the warp-specialised kernel (id 6): 9..24 MOs with the 24 columns spread over three warp columns, so a thread
 // holds 20 accumulators instead of 60 and two CTAs (24 warps) are resident per SM instead of one (8 warps); measured on
-// benzene NCIPLOT 200^3: 20.9 ms against 22.0 ms for S3 (P = 64 and P = 16 variants of the same idea were slower)
+// benzene NCIPLOT 200^3: 20.6 ms against 22.0 ms for S3 (P = 64 and P = 16 variants of the same idea were slower: P = 16
+// with four CTAs per SM 22.8 ms, P = 32 with three CTAs (56 registers, spilling) 33.6 ms; tools/probe_nci.py)
 #define C2_WFN_CONFIGS2(X) \
   X(7, "S3w", 4, 3, 3, 12, 2) \
   X(8, "M2", 2, 4, 8, 16, 2)

@@ -1,0 +1,24 @@
+"""Development probe: benzene NCIPLOT 200^3 (BASELINE config 2) through forced wavefunction kernel configurations."""
+import os, sys
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'tests'))
+import cases
+from critic2_b200 import gpu, drivers
+gpu.init_devices([0])
+f = cases.golden_wfn("benzene-adz"); st = cases.mol_structure(f)
+x0, xmat, ns = drivers.nci_grid(st, nstep=(200, 200, 200))
+n = 200 ** 3
+crho = torch.zeros(n, dtype=torch.float64, device="cuda"); cgrad = torch.zeros_like(crho)
+s = torch.cuda.current_stream().cuda_stream
+ref = None
+for cfg in [int(v) for v in os.environ.get("PROBE_CFG", "7,1").split(",")]:
+    gpu.set_option("wfn_cfg", cfg)
+    fld = gpu.WfnField(f, st)
+    for rep in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fld.nci_dev(x0, xmat, ns, crho, cgrad, stream=s); e1.record(); torch.cuda.synchronize()
+    r = crho.cpu().numpy()
+    if ref is None: ref = r
+    print(f"cfg {cfg} {fld.config()} {e0.elapsed_time(e1):8.3f} ms maxdiff {np.abs(r-ref).max():.2e}", flush=True)
+    fld.close()
