@@ -21,6 +21,7 @@ std::vector<int> g_devs;
 int g_force_cfg = -1;
 int g_fmt_force_exact = 0;
 int g_super = 8;
+int g_nci_two_pass = 1;
 
 int fail(int code, const std::string &msg) {
   g_err = msg;
@@ -78,6 +79,9 @@ struct Replica {
   // scratch of the core pre-pass (f%usecore): nd raw sums per point of the evaluated range, grow-only
   double *corebuf = nullptr;
   size_t corebuf_n = 0;
+  // scratch of the two-pass NCIPLOT evaluation: ten raw sums per point of the evaluated range, grow-only
+  double *rawbuf = nullptr;
+  size_t rawbuf_n = 0;
 };
 
 struct Handle {
@@ -154,6 +158,7 @@ int c2gpu_set_option(const char *name, int value) {
   if (!name) return 1;
   if (!strcmp(name, "wfn_cfg")) { g_force_cfg = value; return 0; }
   if (!strcmp(name, "super")) { if (value < 4 || value % 4) return 1; g_super = value; return 0; }
+  if (!strcmp(name, "nci_two_pass")) { g_nci_two_pass = value; return 0; }   // development: A/B of the NCIPLOT epilogue
   if (!strcmp(name, "fmt_force_exact")) { g_fmt_force_exact = value; return 0; }   // tests: big-integer rounding path
   return 1;
 }
@@ -166,6 +171,7 @@ int c2gpu_destroy(void *handle) {
     for (void *p : r.allocs) cudaFree(p);
     for (double *p : r.outbuf) cudaFree(p);
     if (r.corebuf) cudaFree(r.corebuf);
+    if (r.rawbuf) cudaFree(r.rawbuf);
     if (r.stream) cudaStreamDestroy(r.stream);
   }
   delete h;

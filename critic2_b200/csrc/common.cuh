@@ -67,7 +67,10 @@ __host__ __device__ inline int grid_nc(const GridDesc &g) { return g.nci_order ?
 // mode 1: NCIPLOT crho/cgrad (src/nci@proc.f90:523-525,553-554); mode 2: point list, C2GPU_RES_LEN doubles per point;
 // mode 3: value only into prop[0] (grd0, src/fieldmod@proc.f90:848-928);
 // mode 4: the raw sums f, gf(3), hs(6) before the tail of grd, component k of point idx at res[k*core_stride + idx]
-//         (k < core_nd) -- the core pre-pass below writes this.
+//         (k < core_nd) -- the core pre-pass below writes this;
+// mode 5: like 4 (all ten components) but AFTER the core has been added and the gradient nullified on a nucleus: the first
+//         pass of the two-pass NCIPLOT evaluation of the block-synchronous wavefunction kernels, whose eigenvalue / RDG
+//         epilogue otherwise runs on P threads while the rest of the CTA waits (nci_epilogue_kernel is the second pass).
 // core != null: f%usecore (src/fieldmod@proc.f90:827-832, :922-925): the core promolecular density and derivatives of
 // the same lattice, written by a mode-4 pre-pass of the promolecular kernel over the core tables cgrid(iz,zpsp(iz)),
 // are added to f, gf, hf BEFORE the nucleus test / gfmod / del2f and the NCIPLOT formulas.

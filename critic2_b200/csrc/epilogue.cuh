@@ -162,6 +162,12 @@ __device__ __forceinline__ void emit_point(const OutDesc &o, size_t idx, double 
     }
   }
   if (isnuc) { gx = 0.0; gy = 0.0; gz = 0.0; }                        // :838
+  if (o.mode == 5) {   // first pass of the two-pass NCIPLOT evaluation: f, gf, hs after the core and the nucleus test
+    double *r = o.res + idx;
+    r[0] = f; r[cs] = gx; r[2 * cs] = gy; r[3 * cs] = gz;
+    r[4 * cs] = h0; r[5 * cs] = h1; r[6 * cs] = h2; r[7 * cs] = h3; r[8 * cs] = h4; r[9 * cs] = h5;
+    return;
+  }
   double gmod = norm2_ref(gx, gy, gz);                                // :839
   double lap = add_rn(add_rn(h0, h1), h2);                   // :840
   if (o.mode == 0) {

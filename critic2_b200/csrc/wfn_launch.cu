@@ -186,6 +186,31 @@ __global__ void __launch_bounds__(256) wfn_count_kernel(WfnDev w, GridDesc g, Ce
   if ((threadIdx.x & 31) == 0 && n) atomicAdd(count, n);
 }
 
+// ---- second pass of the two-pass NCIPLOT evaluation: eigenvalues, RDG and sign(lambda2)*rho (src/nci@proc.f90:523-525,
+// 553-554) of every point the first pass owned, one thread per point ------------------------------------------------
+__global__ void __launch_bounds__(256) nci_epilogue_kernel(GridDesc g, OutDesc o, const double *raw, size_t stride,
+                                                            double nci_const) {
+  const int na = grid_na(g), nb = grid_nb(g);
+  const size_t npl = (size_t)na * nb;
+  const size_t q = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (q >= npl * (size_t)(g.c1 - g.c0)) return;
+  const int c = g.c0 + (int)(q / npl), b = (int)((q % npl) / na);
+  if (!tile_owned(g, b, c)) return;
+  const size_t idx = q + (size_t)g.c0 * npl;
+  const double *r = raw + idx;
+  emit_point(o, idx, r[0], r[stride], r[2 * stride], r[3 * stride], r[4 * stride], r[5 * stride], r[6 * stride],
+             r[7 * stride], r[8 * stride], r[9 * stride], false, nci_const);
+}
+
+cudaError_t nci_epilogue_launch(const GridDesc &g, const OutDesc &o, const double *raw, size_t stride, double nci_const,
+                                cudaStream_t st) {
+  const size_t ntot = (size_t)grid_na(g) * grid_nb(g) * (size_t)(g.c1 - g.c0);
+  if (ntot == 0) return cudaSuccess;
+  nci_epilogue_kernel<<<(unsigned)((ntot + 255) / 256), 256, 0, st>>>(g, o, raw, stride, nci_const);
+  g_launches++;
+  return cudaGetLastError();
+}
+
 cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &xf, unsigned long long *count,
                              cudaStream_t st) {
   size_t ntot = (size_t)grid_na(g) * grid_nb(g) * (size_t)(g.c1 - g.c0);

@@ -6,6 +6,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'tests'))
 import cases
 from critic2_b200 import gpu, drivers
 gpu.init_devices([0])
+gpu.set_option("nci_two_pass", int(os.environ.get("NCI_TWO_PASS", "1")))
 f = cases.golden_wfn("benzene-adz"); st = cases.mol_structure(f)
 x0, xmat, ns = drivers.nci_grid(st, nstep=(200, 200, 200))
 n = 200 ** 3
