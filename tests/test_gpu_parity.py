@@ -609,3 +609,40 @@ def test_gkin_and_mo_values_on_point_lists(G, O, name, cfg):
     assert np.array_equal(out[:, 0], np.ones(len(pts))) and np.array_equal(out[:, 3], gk)
     check_rho(out[:, 1], rres[:, 0])
     assert np.array_equal(out[:, 4], fld.mo_points(pts, 1))
+
+
+def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
+    """c2gpu_nci_grid_dev_part through a block-synchronous kernel: the second-pass epilogue kernel must finish exactly the
+    points of the x-layers the part owns (others stay untouched), and the parts reproduce the one-launch result bit for bit;
+    the one-pass evaluation (development switch) gives the same numbers."""
+    import torch
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz")
+    st = cases.mol_structure(f)
+    fld = G.WfnField(f, st)
+    assert fld.config()["cfg"] == 7
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(27, 19, 22))
+    npt = int(np.prod(ns))
+    mk = lambda v: torch.full((npt,), v, dtype=torch.float64, device="cuda")
+    full_rho, full_grad = mk(0.0), mk(0.0)
+    fld.nci_dev(x0, xmat, ns, full_rho, full_grad)
+    acc_rho, acc_grad, cover = mk(0.0), mk(0.0), mk(0.0)
+    for part in range(3):
+        crho, cgrad = mk(float("nan")), mk(float("nan"))
+        fld.nci_dev_part(x0, xmat, ns, crho, cgrad, part, 3)
+        torch.cuda.synchronize()
+        own = ~torch.isnan(crho)
+        assert torch.equal(own, ~torch.isnan(cgrad))
+        cover += own.double()
+        acc_rho += torch.nan_to_num(crho, nan=0.0)
+        acc_grad += torch.nan_to_num(cgrad, nan=0.0)
+    assert bool((cover == 1.0).all())
+    assert torch.equal(acc_rho, full_rho) and torch.equal(acc_grad, full_grad)
+    G.set_option("nci_two_pass", 0)
+    try:
+        one_rho, one_grad = mk(0.0), mk(0.0)
+        fld.nci_dev(x0, xmat, ns, one_rho, one_grad)
+        torch.cuda.synchronize()
+    finally:
+        G.set_option("nci_two_pass", 1)
+    assert torch.equal(one_rho, full_rho) and torch.equal(one_grad, full_grad)
