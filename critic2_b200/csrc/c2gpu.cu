@@ -163,6 +163,8 @@ int c2gpu_set_option(const char *name, int value) {
   return 1;
 }
 
+int c2gpu_wfn_choose_config(int nmoocc) { return wfn_choose_config(nmoocc, -1); }
+
 int c2gpu_destroy(void *handle) {
   Handle *h = static_cast<Handle *>(handle);
   if (!h) return 0;
