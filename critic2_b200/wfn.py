@@ -449,3 +449,101 @@ def write_wfx(f: Molwfn, path: str, title: str = "synthetic") -> None:
             block(fh, "EDF Primitive Types", f.itype_edf, "%d", 20)
             block(fh, "EDF Primitive Exponents", f.e_edf, "%.14E", 5)
             block(fh, "EDF Primitive Coefficients", f.c_edf, "%.14E", 5)
+
+
+# ---- AIMPAC .wfn: read_wfn, wfn_private@proc.F90:648-771 (fixed formats 101-106 at :764-769) ---------------------------
+_ELEM = ("H He Li Be B C N O F Ne Na Mg Al Si P S Cl Ar K Ca Sc Ti V Cr Mn Fe Co Ni Cu Zn Ga Ge As Se Br Kr Rb Sr Y Zr Nb "
+         "Mo Tc Ru Rh Pd Ag Cd In Sn Sb Te I Xe").split()
+
+
+def _fortran_e(x: float, w: int, d: int) -> str:
+    """Fortran Ew.d edit descriptor (0.dddddE+xx); 'D' exponents are accepted on input (Gaussian writes them)."""
+    if x == 0.0:
+        return ("0." + "0" * d + "E+00").rjust(w)
+    m, ex = ("%.*E" % (d - 1, x)).split("E")
+    digits = m.replace(".", "").replace("-", "")
+    return (("-" if x < 0 else "") + "0." + digits + "E%+03d" % (int(ex) + 1)).rjust(w)
+
+
+def read_wfn(path: str) -> Molwfn:
+    """LOAD file.wfn.  Columns follow the reference's formats: 101 (4X,A4,10X,3(I5,15X)), 106 (2X,A2,20X,3F12.8,10X,F5.1),
+    102 (20X,20I3), 103 (10X,5E14.7), 104 (35X,F12.7,15X,F12.6), 105 (5E16.8)."""
+    with open(path) as fh:
+        lines = fh.read().split("\n")
+    num = lambda s: float(s.replace("D", "E").replace("d", "E"))
+    hdr = lines[1]
+    nmoocc, npri, nat = int(hdr[18:23]), int(hdr[38:43]), int(hdr[58:63])
+    xyz, z = np.zeros((nat, 3)), np.zeros(nat, np.int32)
+    for i in range(nat):
+        l = lines[2 + i]
+        xyz[i] = [num(l[24 + 12 * k:36 + 12 * k]) for k in range(3)]
+        z[i] = int(round(num(l[70:75])))              # the nuclear charge column (ECP files: element symbol wins, :681-682)
+    pos = 2 + nat
+
+    def fixed(n, skip, width, per, conv):
+        nonlocal pos
+        out = []
+        while len(out) < n:
+            l = lines[pos][skip:]
+            pos += 1
+            out.extend(conv(l[k * width:(k + 1) * width]) for k in range(min(per, n - len(out))))
+        return out
+
+    icenter = np.array(fixed(npri, 20, 3, 20, int), np.int32)
+    itype = np.array(fixed(npri, 20, 3, 20, int), np.int32)
+    if (itype > 56).any():
+        raise ValueError("read_wfn: primitive type not supported")
+    e = np.array(fixed(npri, 10, 14, 5, num))
+    while not lines[pos].startswith("MO"):              # ECP records, :707-711
+        pos += 1
+    occ, ene, cmo = np.zeros(nmoocc), np.zeros(nmoocc), np.zeros((npri, nmoocc))
+    for i in range(nmoocc):
+        l = lines[pos]
+        pos += 1
+        occ[i], ene[i] = num(l[35:47]), num(l[62:74])
+        cmo[:, i] = fixed(npri, 0, 16, 5, num)
+    ioc = np.rint(occ)
+    nalpha, found = -1, False
+    for i in range(1, nmoocc):                          # alpha/beta boundary: orbital energy drops by > 1e-3 (:741-745)
+        if ene[i] < ene[i - 1] - 1e-3:
+            nalpha, found = i, True
+    if (np.abs(ioc - occ) > 1e-10).any():
+        wfntyp, nalpha = WFN_FRAC, 0
+    elif not (ioc == 1).any():
+        wfntyp = WFN_RHF
+    elif not (ioc == 2).any():
+        wfntyp = WFN_UHF
+        if not found:
+            nalpha = nmoocc
+    else:
+        raise ValueError("read_wfn: restricted-open wfn files not supported")
+    f = Molwfn(natom=nat, xyz=xyz, z=z, icenter=icenter, itype=itype, e=e, occ=occ, cmo=np.ascontiguousarray(cmo),
+               nmoocc=nmoocc, wfntyp=wfntyp, nalpha=nalpha)
+    prune_primitives(f)
+    complete_struct(f)
+    return f
+
+
+def write_wfn(f: Molwfn, path: str, energies=None, title: str = "synthetic") -> None:
+    """Write an AIMPAC .wfn the reference's read_wfn accepts (single-precision text: E14.7 exponents, E16.8 coefficients)."""
+    ene = np.arange(f.nmoocc, dtype=float) * 0.01 - 10.0 if energies is None else np.asarray(energies, float)
+    with open(path, "w") as fh:
+        fh.write(title + "\n")
+        fh.write("GAUSSIAN".ljust(18) + "%5d" % f.nmoocc + " MOL ORBITALS  " + "%5d" % f.npri + " PRIMITIVES    "
+                 + "%5d" % f.natom + " NUCLEI\n")
+        for i in range(f.natom):
+            el = _ELEM[int(f.z[i]) - 1]
+            fh.write("  %-2s%4d    (CENTRE%3d) " % (el, i + 1, i + 1) + "".join("%12.8f" % v for v in f.xyz[i])
+                     + "  CHARGE =%5.1f\n" % float(f.z[i]))
+        for name, arr in (("CENTRE ASSIGNMENTS  ", f.icenter), ("TYPE ASSIGNMENTS    ", f.itype)):
+            for k in range(0, f.npri, 20):
+                fh.write(name + "".join("%3d" % v for v in arr[k:k + 20]) + "\n")
+        for k in range(0, f.npri, 5):
+            fh.write("EXPONENTS ".ljust(10) + "".join(_fortran_e(float(v), 14, 7) for v in f.e[k:k + 5]) + "\n")
+        for i in range(f.nmoocc):
+            fh.write(("MO%5d" % (i + 1)).ljust(16) + "MO 0.0".ljust(8) + "OCC NO = ".rjust(11) + "%12.7f" % f.occ[i]
+                     + "  ORB. ENERGY =" + "%12.6f" % ene[i] + "\n")
+            c = f.cmo[:, i]
+            for k in range(0, f.npri, 5):
+                fh.write("".join(_fortran_e(float(v), 16, 8) for v in c[k:k + 5]) + "\n")
+        fh.write("END DATA\n")

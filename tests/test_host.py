@@ -207,3 +207,29 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     assert [pick(n) for n in (193, 224)] == [3, 3]
     assert pick(250) == 8
     assert [pick(n) for n in (300, 780, 3120)] == [6, 6, 6]      # BASELINE configs 4 and 5
+
+
+def test_aimpac_wfn_round_trip(tmp_path):
+    """read_wfn (wfn_private@proc.F90:648-771): the fixed-column formats 101-106, the wavefunction-type rules and the
+    alpha/beta boundary from the orbital-energy drop, through a write/read round trip at the file's text precision."""
+    from critic2_b200 import synth, wfn
+    f = cases.golden_wfn("h2o-wfx")
+    p = str(tmp_path / "h2o.wfn")
+    wfn.write_wfn(f, p)
+    lines = open(p).read().split("\n")
+    assert lines[1] == "GAUSSIAN              5 MOL ORBITALS     59 PRIMITIVES        3 NUCLEI"
+    assert lines[2][2:4] == "O " and float(lines[2][70:75]) == 8.0 and len(lines[2]) == 75
+    g = wfn.read_wfn(p)
+    assert (g.npri, g.nmoocc, g.wfntyp) == (f.npri, f.nmoocc, wfn.WFN_RHF)
+    assert np.array_equal(g.icenter, f.icenter) and np.array_equal(g.itype, f.itype) and np.array_equal(g.z, f.z)
+    np.testing.assert_allclose(g.e, f.e, rtol=1e-6)
+    np.testing.assert_allclose(g.cmo, f.cmo, rtol=0, atol=1e-7 * np.abs(f.cmo).max())
+    np.testing.assert_allclose(g.xyz, f.xyz, atol=1e-8)
+    np.testing.assert_allclose(g.dran, f.dran, rtol=1e-6)
+    # unrestricted: occupations 1, alpha block first; the beta block starts where the orbital energy drops (:741-745)
+    u = synth.small_synthetic(uhf=True)
+    ene = np.concatenate([np.linspace(-5.0, -0.3, u.nalpha), np.linspace(-4.9, -0.4, u.nmoocc - u.nalpha)])
+    q = str(tmp_path / "u.wfn")
+    wfn.write_wfn(u, q, energies=ene)
+    v = wfn.read_wfn(q)
+    assert v.wfntyp == wfn.WFN_UHF and v.nalpha == u.nalpha and v.npri == u.npri
