@@ -93,10 +93,11 @@ int wfn_choose_config(int nmo, int force) {
   //   M2      57    111   111   164   164   217
   //   L      103    103   197   197   197   197
   //   WS     148    148   200   200   200   200
+  // L1 is L with 8-point sub-tiles and two CTAs per SM (224 threads each): 100.7 / 194.3 ms where L takes 103.2 / 197.9.
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
-  const int tM = 54 * bM + 3, tL = 97 * bL + 6, tW = 96 + 52 * bL;
+  const int tM = 54 * bM + 3, tL = 95 * bL + 6, tW = 96 + 52 * bL;
   if (tM <= tL && tM <= tW) return 8;
-  return tL <= tW ? 3 : 6;
+  return tL <= tW ? 4 : 6;
 }
 
 template <class C>

@@ -199,7 +199,7 @@ int c2gpu_promol_count_active(void *h, const double x0[3], const double xd[9], c
                               double *sum_nat);
 /* Kernel configuration chosen for a wavefunction handle: points per tile, MO columns per block, blocks, threads. */
 int c2gpu_wfn_config(void *h, int cfg[8]);
-/* The configuration id wfn_create picks for an occupied-MO count (no device needed): 0 S1, 7 S3w, 8 M2, 3 L, 6 WS. */
+/* The configuration id wfn_create picks for an occupied-MO count (no device needed): 0 S1, 7 S3w, 8 M2, 4 L1, 6 WS. */
 int c2gpu_wfn_choose_config(int nmoocc);
 /* Override tunables (name/value); used by bench sweeps.  Unknown names return 1. */
 int c2gpu_set_option(const char *name, int value);
