@@ -400,3 +400,32 @@ def test_mo_values_and_gkin_against_dense_numpy():
     assert np.max(np.abs(res[:, 17] - gk) / gk) < 1e-7
     far = st.r[0] + np.array([[60.0, 0.0, 0.0]])
     assert fld.mo_points(far, 1, periodic=False)[0] == 0.0
+
+
+def test_nciplot_formulas_on_a_single_gaussian():
+    """nciplot's per-point quantities (nci@proc.f90:86-87,523-525,553-554) in closed form: one s Gaussian, one doubly
+    occupied MO: rho = 2 c^2 exp(-2 a r^2); the Hessian eigenvalues are -4a rho (twice, tangential) and
+    (16 a^2 r^2 - 4a) rho (radial), so lambda2 < 0 everywhere off the nucleus; s = |grad rho| / (2 (3 pi^2)^(1/3) rho^(4/3))."""
+    from critic2_b200.wfn import Molwfn, complete_struct
+    a, c = 0.45, 0.8
+    f = Molwfn(natom=1, xyz=np.zeros((1, 3)), z=np.array([2], np.int32), icenter=np.array([1], np.int32),
+               itype=np.array([1], np.int32), e=np.array([a]), occ=np.array([2.0]), cmo=np.array([[c]]), nmoocc=1)
+    complete_struct(f)
+    st = cases.mol_structure(f)
+    fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
+    x0 = st.r[0] + np.array([0.13, -0.21, 0.05])
+    xmat = np.diag([0.17, 0.11, 0.19])
+    ns = (5, 6, 4)
+    crho, cgrad, _ = fld.nci(x0, xmat, ns)
+    i, j, k = np.meshgrid(np.arange(ns[0]), np.arange(ns[1]), np.arange(ns[2]), indexing="ij")
+    p = x0[None, None, None, :] + i[..., None] * xmat[:, 0] + j[..., None] * xmat[:, 1] + k[..., None] * xmat[:, 2] - st.r[0]
+    r2 = (p ** 2).sum(-1)
+    rho = 2 * c * c * np.exp(-2 * a * r2)
+    np.testing.assert_allclose(crho, -100.0 * rho, rtol=1e-12)           # sign(lambda2) = -1
+    s = 4 * a * np.sqrt(r2) * rho / (2.0 * (3.0 * np.pi ** 2) ** (1.0 / 3.0) * rho ** (4.0 / 3.0))
+    np.testing.assert_allclose(cgrad, s, rtol=1e-11)
+    h = fld.grd(x0, 2, True)[4:13].reshape(3, 3)
+    ev = oracle.eig(h)
+    r0 = ((x0 - st.r[0]) ** 2).sum()
+    rho0 = 2 * c * c * np.exp(-2 * a * r0)
+    np.testing.assert_allclose(ev, sorted([-4 * a * rho0, -4 * a * rho0, (16 * a * a * r0 - 4 * a) * rho0]), rtol=1e-10)
