@@ -233,3 +233,34 @@ def test_aimpac_wfn_round_trip(tmp_path):
     wfn.write_wfn(u, q, energies=ene)
     v = wfn.read_wfn(q)
     assert v.wfntyp == wfn.WFN_UHF and v.nalpha == u.nalpha and v.npri == u.npri
+
+
+def test_fortran_shim_matches_the_c_header():
+    """fortran/gpu_interface.f90 cannot be compiled here (no Fortran compiler), so at least its bind(c) interfaces are
+    checked against include/c2gpu.h: every bound name is declared in the header with the same number of arguments, and
+    pass-by-value dummies are exactly the header's non-pointer parameters."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "c2gpu.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    cdecl = {}
+    for m in re.finditer(r"\b(?:int|long)\s+(c2gpu_\w+)\s*\(([^;]*?)\)\s*;", hdr, flags=re.S):
+        args = [a.strip() for a in m.group(2).replace("\n", " ").split(",")]
+        args = [] if args == ["void"] else args
+        cdecl[m.group(1)] = ["*" in a or "[" in a for a in args]          # True = pointer / array parameter
+    src = open(os.path.join(root, "fortran", "gpu_interface.f90")).read()
+    src = re.sub(r"&\s*\n\s*&?", "", src)                                   # join continuation lines
+    blocks = re.findall(r"function\s+(c2gpu_\w+)\s*\(([^)]*)\)\s*bind\(c,name=\"(\w+)\"\)(.*?)end function", src, flags=re.S)
+    assert len(blocks) >= 15
+    for fname, arglist, cname, body in blocks:
+        assert fname == cname and cname in cdecl, cname
+        names = [a.strip() for a in arglist.split(",") if a.strip()]
+        assert len(names) == len(cdecl[cname]), f"{cname}: {len(names)} Fortran dummies vs {len(cdecl[cname])} C parameters"
+        byval = set()
+        for line in body.split("\n"):
+            if "value" in line.split("::")[0]:
+                byval.update(n.strip().split("(")[0] for n in line.split("::")[1].split(","))
+        for n, is_ptr in zip(names, cdecl[cname]):
+            # type(c_ptr), value carries a C pointer by value: allowed for pointer parameters (handles, nullable arrays)
+            if not is_ptr:
+                assert n in byval, f"{cname}: {n} must be passed by value"
