@@ -113,9 +113,24 @@ __global__ void __launch_bounds__(1024) cut_scan_kernel(int nblk, const unsigned
     if (threadIdx.x == 1023) s_carry = off + incl;
     __syncthreads();
   }
+  // sums of the block partials in a fixed order (reproducible for a given grid): every thread adds a contiguous run of
+  // blocks sequentially, lanes are folded by a butterfly, thread 0 adds the 32 warp sums in order
+  __shared__ double s_p[3][32];
+  const int chunk = (nblk + 1023) / 1024;
+  double s0 = 0, s1 = 0, s2 = 0;
+  for (int i = threadIdx.x * chunk; i < min(nblk, (threadIdx.x + 1) * chunk); i++) {
+    s0 += bsum[3 * (size_t)i]; s1 += bsum[3 * (size_t)i + 1]; s2 += bsum[3 * (size_t)i + 2];
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    s0 += __shfl_xor_sync(~0u, s0, o);
+    s1 += __shfl_xor_sync(~0u, s1, o);
+    s2 += __shfl_xor_sync(~0u, s2, o);
+  }
+  if (lane == 0) { s_p[0][warp] = s0; s_p[1][warp] = s1; s_p[2][warp] = s2; }
+  __syncthreads();
   if (threadIdx.x == 0) {
-    double s0 = 0, s1 = 0, s2 = 0;
-    for (int i = 0; i < nblk; i++) { s0 += bsum[3 * (size_t)i]; s1 += bsum[3 * (size_t)i + 1]; s2 += bsum[3 * (size_t)i + 2]; }
+    s0 = s1 = s2 = 0;
+    for (int w = 0; w < 32; w++) { s0 += s_p[0][w]; s1 += s_p[1][w]; s2 += s_p[2][w]; }
     out[0] = (double)s_carry; out[1] = s0; out[2] = s1; out[3] = s2;
   }
 }
@@ -159,11 +174,25 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
             nfrag, rhofrag, rhoparam, rhoparam2};
   int nblk = (int)((npts + CUT_BLK - 1) / CUT_BLK);
   // one scratch allocation: out[4] | bsum[3*nblk] | boff[nblk] (64-bit) | bcount[nblk]
-  unsigned char *scr = nullptr;
+  // kept per device between calls (grow-only): cudaMalloc + cudaFree cost more than the pass itself on a 200^3 grid
+  static unsigned char *s_scr[64] = {nullptr};
+  static size_t s_cap[64] = {0};
   const size_t o_bsum = 4 * sizeof(double), o_boff = o_bsum + sizeof(double) * 3 * (size_t)nblk;
   const size_t o_bcount = o_boff + sizeof(unsigned long long) * (size_t)nblk;
+  const size_t need = o_bcount + sizeof(unsigned) * (size_t)nblk;
   cudaError_t e;
-  if ((e = cudaMalloc(&scr, o_bcount + sizeof(unsigned) * (size_t)nblk)) != cudaSuccess) return e;
+  int dev = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (s_cap[dev] < need) {
+    if (s_scr[dev]) cudaFree(s_scr[dev]);
+    s_scr[dev] = nullptr; s_cap[dev] = 0;
+    void *d = nullptr;
+    if ((e = cudaMalloc(&d, need + need / 2)) != cudaSuccess) return e;
+    s_scr[dev] = static_cast<unsigned char *>(d);
+    s_cap[dev] = need + need / 2;
+  }
+  unsigned char *scr = s_scr[dev];
   double *out = reinterpret_cast<double *>(scr), *bsum = reinterpret_cast<double *>(scr + o_bsum);
   unsigned long long *boff = reinterpret_cast<unsigned long long *>(scr + o_boff);
   unsigned *bcount = reinterpret_cast<unsigned *>(scr + o_bcount);
@@ -174,7 +203,6 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
   double h[4];
   e = cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(scr);
   if (e != cudaSuccess) return e;
   *ndat = (long)h[0];
   raw_sums[0] = h[1]; raw_sums[1] = h[2]; raw_sums[2] = h[3];
