@@ -22,7 +22,9 @@ int g_force_cfg = -1;
 int g_fmt_force_exact = 0;
 int g_super = 8;
 int g_nci_two_pass = 1;
-int g_empty_fast = 0;   // block-synchronous kernels: fast path for super-tiles without active shells
+int g_empty_fast = 0;   // block-synchronous kernels: fast path for super-tiles without active shells.  Parity-green when on
+                        // (54 GPU tests), but no gain on BASELINE configs 1 and 2 (1.480 / 17.25 ms either way: the diffuse
+                        // aug- functions reach every super-tile of those grids), so it stays off
 
 int fail(int code, const std::string &msg) {
   g_err = msg;
