@@ -323,7 +323,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       }
       // tile complete: make the generic-proxy global writes visible to the streamer's bulk (async-proxy) loads
       __threadfence();
-      fence_proxy_async();
+      fence_proxy_async_global();
       named_bar_sync(2, NGT);
       if (gtid == 0) {
         WsTileDesc &td = S.tdesc[buf];
@@ -356,7 +356,7 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
   for (unsigned tcount = 0;; tcount++) {
     const int buf = tcount & 1;
     mbar_wait(&S.ready[buf], (tcount >> 1) & 1u);
-    fence_proxy_async();
+    fence_proxy_async_global();
     const WsTileDesc td = S.tdesc[buf];
     if (td.flags & 1) break;
     const int2 *pr_list = pr_list0 + (size_t)buf * p.prim_cap;

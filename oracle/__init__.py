@@ -70,7 +70,8 @@ def lib():
         L.orc_text_record_bytes.restype = C.c_long
         L.orc_text_record_bytes.argtypes = [C.c_int, C.c_int]
         L.orc_cube_text.argtypes = [dp, ip, C.c_int, C.c_int, C.c_char_p, C.c_int]
-        L.orc_promolecular_grid.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), ip, dp, C.c_int]
+        L.orc_promolecular_grid.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), ip, C.c_char_p, dp, C.c_int]
+        L.orc_promol_nat_points.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_long, dp, C.c_char_p, C.POINTER(C.c_long), C.c_int]
         L.orc_grd_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
         L.orc_mo_points.argtypes = [C.c_void_p, C.c_long, dp, C.c_int, C.c_int, dp, C.c_int]
         L.orc_nact_points.argtypes = [C.c_void_p, C.c_void_p, C.c_long, dp, C.POINTER(C.c_long), C.c_int]
@@ -307,11 +308,23 @@ def eig(h):
     return ev
 
 
-def promolecular_grid(env: Environ, grids: Grid1Set, n, nthreads=0):
+def promolecular_grid(env: Environ, grids: Grid1Set, n, nthreads=0, fragmask=None):
+    """crystal%promolecular_grid(f, n, zpsp, fr): grids = agrid, or the core selection cgrid(iz, zpsp(iz)) (tables with q);
+    fragmask: per cell atom, the `fr` argument."""
     n = _i32(n)
     out = np.zeros(int(n[0]) * int(n[1]) * int(n[2]))
-    lib().orc_promolecular_grid(env.ptr, grids.arr, _i(n), _d(out), nthreads)
+    fm = None if fragmask is None else np.ascontiguousarray(fragmask, np.uint8).tobytes()
+    lib().orc_promolecular_grid(env.ptr, grids.arr, _i(n), fm, _d(out), nthreads)
     return out.reshape(n[2], n[1], n[0])
+
+
+def promol_nat_points(env: Environ, grids: Grid1Set, pts, nthreads=0, fragmask=None):
+    """atoms entering promolecular's radial sum at each point (Cartesian bohr)"""
+    pts = _f64(pts)
+    out = np.zeros(pts.shape[0], np.int64)
+    fm = None if fragmask is None else np.ascontiguousarray(fragmask, np.uint8).tobytes()
+    lib().orc_promol_nat_points(env.ptr, grids.arr, pts.shape[0], _d(pts), fm, out.ctypes.data_as(C.POINTER(C.c_long)), nthreads)
+    return out
 
 
 from . import cube_text  # noqa: E402,F401  (formatted-output restatement, pure Python)

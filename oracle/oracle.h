@@ -147,7 +147,11 @@ long orc_nci_cutoffs_frag(const int *nstep, double *crho, double *cgrad, const d
                           double rhoplot, const double *srhorange, int onlyneg, double rho_void, double omega,
                           double *sums, double *dat, long maxdat);
 /* promolecular_grid (src/crystalmod@proc.f90:5118-5158): whole-cell grid at fractional nodes (i-1)/n, nder=0 */
-void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, double *out, int nthreads);
+void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, const unsigned char *fragmask,
+                           double *out, int nthreads);
+/* number of atoms entering the radial sum of promolecular at each point (the pairs F_pro of SURVEY 8(d) counts) */
+void orc_promol_nat_points(const orc_environ *e, orc_grid1 *const *agrid, long npts, const double *pts,
+                           const unsigned char *fragmask, long *nat, int nthreads);
 /* formatted cube bodies (oracle_text.c): writegrid_cube / write_cube_body / .dat text */
 long orc_text_record_bytes(int nval, int fmt);
 void orc_cube_text(const double *g, const int *n, int fmt, int order, char *text, int nthreads);

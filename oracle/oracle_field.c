@@ -392,7 +392,8 @@ long orc_nci_cutoffs(const int *nstep, double *crho, double *cgrad, const double
 }
 
 /* promolecular_grid crystalmod@proc.f90:5118-5158 */
-void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, double *out, int nthreads) {
+void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const int *n, const unsigned char *fragmask,
+                           double *out, int nthreads) {
 #ifdef _OPENMP
   if (nthreads > 0) omp_set_num_threads(nthreads);
 #endif
@@ -406,7 +407,7 @@ void orc_promolecular_grid(const orc_environ *e, orc_grid1 *const *agrid, const 
         if (!e->ismolecule)
           for (int d = 0; d < 3; d++) xr[d] = xr[d] - floor(xr[d]);
         orc_matvec(e->m_xr2c, xr, xc);
-        orc_promolecular(e, agrid, xc, 0, NULL, &rho, g, h);
+        orc_promolecular(e, agrid, xc, 0, fragmask, &rho, g, h);   /* fr: :5149 */
         out[(size_t)i + (size_t)n[0] * ((size_t)j + (size_t)n[1] * k)] = rho;
       }
 }

@@ -9,6 +9,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 orc_grid1 *orc_grid1_from_table(int z, int qat, int ngrid, double a, double b, const double *r, const double *f,
                                 const double *fp, const double *fpp) {
@@ -202,4 +205,47 @@ void orc_promolecular(const orc_environ *e, orc_grid1 *const *agrid, const doubl
   }
   free(nid);
   free(dist);
+}
+
+/* The atoms of promolecular's sum loop (:1284-1300) that reach interp: inside list_near_atoms' species cutoff
+ * min(cutrad, rmax), in the fragment, with an initialised table.  x0 Cartesian; folded like :1242-1243. */
+static long orc_promol_nat(const orc_environ *e, orc_grid1 *const *agrid, const double *x0, const unsigned char *fragmask) {
+  double xc[3] = {x0[0], x0[1], x0[2]};
+  orc_center_cart(e, xc, NULL);
+  double *rcutmax = calloc(e->nspc, sizeof(double));
+  for (int i = 0; i < e->nspc; i++) {
+    int iz = e->zspc[i];
+    if (iz == 0 || iz > 118) continue;
+    const orc_grid1 *g = agrid[iz];
+    if (g && g->isinit) rcutmax[i] = fmin(orc_cutrad(iz), g->rmax);
+    else rcutmax[i] = orc_cutrad(iz);
+  }
+  int *nid = malloc(sizeof(int) * e->n);
+  double *dist = malloc(sizeof(double) * e->n);
+  int nat, lvec[3];
+  orc_list_near_atoms(e, xc, 1, rcutmax, &nat, nid, dist, lvec);
+  free(rcutmax);
+  long cnt = 0;
+  for (int ii = 0; ii < nat; ii++) {
+    int i = nid[ii];
+    if (fragmask && !fragmask[e->cidx[i] - 1]) continue;
+    int iz = e->zspc[e->is[i] - 1];
+    if (iz == 0 || iz > 118) continue;
+    if (dist[ii] > orc_cutrad(iz)) continue;
+    const orc_grid1 *g = agrid[iz];
+    if (!g || !g->isinit) continue;
+    cnt++;
+  }
+  free(nid);
+  free(dist);
+  return cnt;
+}
+
+void orc_promol_nat_points(const orc_environ *e, orc_grid1 *const *agrid, long npts, const double *pts,
+                           const unsigned char *fragmask, long *nat, int nthreads) {
+#ifdef _OPENMP
+  if (nthreads > 0) omp_set_num_threads(nthreads);
+#endif
+#pragma omp parallel for schedule(dynamic, 64)
+  for (long p = 0; p < npts; p++) nat[p] = orc_promol_nat(e, agrid, pts + 3 * p, fragmask);
 }

@@ -646,3 +646,178 @@ def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
     finally:
         G.set_option("nci_two_pass", 1)
     assert torch.equal(one_rho, full_rho) and torch.equal(one_grad, full_grad)
+
+
+# ---- round 2: the multi-MO-block paths of the tensor-core kernels -------------------------------------------------------
+@pytest.mark.parametrize("cfg", [3, 4, 6, 8])
+@pytest.mark.parametrize("nmo", [113, 300])
+@pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
+def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
+    """More MOs than one block holds (the loop wfn_private@proc.F90:2771-2776 cut into column blocks): 113 MOs = 2 blocks of
+    112 with a one-column last block, 300 MOs = 3 blocks of 112 (5 of 64 for M2).  In the warp-specialised kernel (cfg 6)
+    this runs the chi-tile cache re-read, both zigzag directions of the chunk walk and the register accumulation of the
+    quadratic forms across blocks; in L / L1 / M2 the per-block recomputation and the fixed-order cross-block sum."""
+    from critic2_b200 import synth
+    f = synth.small_synthetic(uhf=(variant != "rhf"), with_edf=(variant != "rhf"), nmo=nmo)
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, (18, 14, 12), margin=3.0)
+    ref = _ofield(O, f, st).cube(x0, xd, nn)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    c = fld.config()
+    assert c["cfg"] == cfg and c["nblk"] == -(-nmo // c["mo_block"]) and c["nblk"] >= 2
+    got = fld.cube(x0, xd, nn)
+    print(cfg, nmo, variant, c["nblk"], _compare_cube(got, ref))
+
+
+@pytest.mark.parametrize("cfg", [4, 6])
+def test_nci_and_points_multi_block(G, O, cfg):
+    """NCIPLOT evaluation and a ragged point list with three MO blocks (classification identical, nuclei flagged)."""
+    from critic2_b200 import drivers, synth
+    f = synth.small_synthetic(nmo=230)
+    st = cases.mol_structure(f)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    assert fld.config()["nblk"] == 3
+    of = _ofield(O, f, st)
+    x0, xmat, ns = drivers.nci_grid(st, nstep=(15, 13, 17))
+    rrho, rgrad, _ = of.nci(x0, xmat, ns)
+    crho, cgrad, _ = fld.nci(x0, xmat, ns)
+    assert _nci_compare(crho, cgrad, rrho, rgrad) == 0
+    rg, cg = rgrad.copy(), cgrad.reshape(-1).copy()
+    _, rdat = O.nci_cutoffs(rrho.copy(), rg, rhocut=1e3, dimcut=50.0)
+    _, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg, rhocut=1e3, dimcut=50.0)
+    assert ndat == len(rdat) and np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
+    rng = np.random.default_rng(7)
+    pts = np.concatenate([st.r[:2], rng.uniform(st.r.min(0) - 2.0, st.r.max(0) + 2.0, (517, 3))])
+    ref = of.grd_points(pts, nder=2, periodic=False)
+    got = fld.points(pts, nder=2, periodic=False)
+    check_rho(got[:, 0], ref[:, 0])
+    check_vec(got[:, 1:4], ref[:, 1:4], "grad", rho=ref[:, 0])
+    check_vec(got[:, 4:13], ref[:, 4:13], "hess", rho=ref[:, 0])
+    assert np.array_equal(got[:, 15] != 0, ref[:, 15] != 0)
+
+
+def test_count_active_matches_oracle(G, O):
+    """The numerators of bench.py's rooflines: c2gpu_wfn_count_active = sum over points of the primitives passing the
+    reference's own screen (wfn_private@proc.F90:2747; oracle orc_nact), c2gpu_promol_count_active = (point, atom) pairs
+    entering the radial sum (environmod@proc.f90:1284-1300)."""
+    from critic2_b200 import drivers, synth
+    for f in (synth.small_synthetic(), cases.golden_wfn("h2o-aqz")):
+        st = cases.mol_structure(f)
+        x0, xd, nn = cases.bbox_grid(st, (19, 13, 11), margin=5.0)
+        fld = G.WfnField(f, st)
+        I, J, K = np.meshgrid(*[np.arange(int(n)) for n in nn], indexing="ij")
+        pts = x0[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ xd.T
+        ref = int(_ofield(O, f, st).nact_points(pts).sum())
+        assert int(fld.count_active(x0, xd, nn)) == ref and ref > 0
+        zsel = pts[:, 2] >= x0[2] + 3 * xd[2, 2] - 1e-9
+        zsel &= pts[:, 2] < x0[2] + 8 * xd[2, 2] - 1e-9
+        assert int(fld.count_active(x0, xd, nn, iz0=3, iz1=8)) == int(_ofield(O, f, st).nact_points(pts[zsel]).sum())
+    st = cases.quartz(1)
+    tabs = cases.tables()
+    o, xq, nq = drivers.cube_grid(st, (13, 11, 9))
+    I, J, K = np.meshgrid(*[np.arange(int(n)) for n in nq], indexing="ij")
+    pts = np.asarray(o)[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ np.asarray(xq).T
+    ref = int(O.promol_nat_points(O.Environ(st), O.Grid1Set(tabs), pts).sum())
+    assert int(G.PromolField(st, tabs).count_active(o, xq, nq, periodic=True)) == ref and ref > 0
+
+
+# ---- round 2: promolecular_grid variants (SURVEY 8(f) rank 3; crystalmod@proc.f90:5118-5158) ---------------------------
+def test_promolecular_grid_core_and_fragment_variants(G, O):
+    """promolecular_grid(f, n, zpsp, fr): LOAD AS CORE (fieldmod@proc.f90:414-431) sums the core tables cgrid(iz, zpsp(iz)),
+    the fragment variant (hirshfeld@proc.f90:49) only the atoms of a fragment; quartz (periodic images) and a molecule."""
+    ct = cases.core_tables()
+    tabs = cases.tables()
+    # crystal, core
+    st = cases.quartz(1)
+    zpsp = {14: 4, 8: 6}
+    n = (15, 14, 17)
+    env = O.Environ(st)
+    otabs = {z: ct[(z, q)] for z, q in zpsp.items()}
+    ref = O.promolecular_grid(env, O.Grid1Set(otabs), n)
+    got = G.core_field(st, ct, zpsp).promolecular_grid(n)
+    check_rho(got, ref, "promolecular_grid(zpsp)")
+    assert ref.max() > 1.0
+    # crystal, only one species has a core (zpsp <= 0 for the other: no table, contributes nothing)
+    ref1 = O.promolecular_grid(env, O.Grid1Set({14: ct[(14, 4)]}), n)
+    got1 = G.core_field(st, ct, {14: 4, 8: 0}).promolecular_grid(n)
+    check_rho(got1, ref1, "promolecular_grid(zpsp, Si only)")
+    # crystal, fragment = the atoms of the first formula unit
+    mask = np.zeros(st.ncell, np.uint8)
+    mask[[0, 3, 4]] = 1
+    reff = O.promolecular_grid(env, O.Grid1Set(tabs), n, fragmask=mask)
+    gotf = G.PromolField(st, tabs, fragmask=mask).promolecular_grid(n)
+    check_rho(gotf, reff, "promolecular_grid(fr)")
+    full = O.promolecular_grid(env, O.Grid1Set(tabs), n)
+    assert (reff < full).any() and reff.max() > 0
+    # molecule (whole molecular cell: mostly exact zeros), core + fragment
+    f = cases.golden_wfn("benzene-adz")
+    sm = cases.mol_structure(f)
+    envm = O.Environ(sm)
+    nm = (21, 19, 11)
+    refm = O.promolecular_grid(envm, O.Grid1Set({6: ct[(6, 4)]}), nm)
+    gotm = G.core_field(sm, ct, {6: 4, 1: 0}).promolecular_grid(nm)
+    check_rho(gotm, refm, "molecular promolecular_grid(zpsp)")
+    maskm = np.zeros(sm.ncell, np.uint8)
+    maskm[:5] = 1
+    check_rho(G.PromolField(sm, tabs, fragmask=maskm).promolecular_grid(nm),
+              O.promolecular_grid(envm, O.Grid1Set(tabs), nm, fragmask=maskm), "molecular promolecular_grid(fr)")
+
+
+# ---- round 2: the single-process, all-devices host path (what the Fortran caller gets from gpu_init -> c2gpu_init(0)) -----
+def test_multi_device_host_path_matches_one_device(G):
+    """host_eval with ndev > 1 (csrc/c2gpu_drivers.inc): layers dealt round-robin over the replicas, per-slab events,
+    interleaved copy-back, core pre-pass and two-pass NCIPLOT under c_nparts > 1 -- bit for bit the one-device result, on
+    ragged grids whose layer count is not a multiple of the device count."""
+    import torch
+    from critic2_b200 import drivers, synth
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs at least two GPUs")
+    tabs, ct = cases.tables(), cases.core_tables()
+    fb = cases.golden_wfn("benzene-adz")
+    sb = cases.mol_structure(fb)
+    fs = synth.small_synthetic(nmo=230)
+    ss = cases.mol_structure(fs)
+    q = cases.quartz(1)
+
+    def run_all():
+        out = {}
+        for cfg, f, st, tag in ((-1, fb, sb, "benzene"), (6, fs, ss, "ws"), (4, fs, ss, "l1")):
+            G.set_option("wfn_cfg", cfg)
+            try:
+                fld = G.WfnField(f, st)
+            finally:
+                G.set_option("wfn_cfg", -1)
+            x0, xd, nn = cases.bbox_grid(st, (21, 19, 8 * (ndev + 1) + 3), margin=3.0)   # ndev + 2 layers, ragged last
+            out[tag + "/cube"] = fld.cube(x0, xd, nn)
+            xn, xm, ns = drivers.nci_grid(st, nstep=(8 * ndev + 5, 14, 13))
+            pro = G.PromolField(st, tabs)
+            out[tag + "/nci"] = dict(zip(("crho", "cgrad", "rhoat"), fld.nci(xn, xm, ns, promol=pro)))
+            if tag == "benzene":
+                fld.set_core(G.core_field(st, ct, {6: 4, 1: 0}))
+                out[tag + "/core cube"] = fld.cube(x0, xd, nn, props=("f", "gmod", "lap"))
+                out[tag + "/core nci"] = dict(zip(("crho", "cgrad"), fld.nci(xn, xm, ns)[:2]))
+        pq = G.PromolField(q, tabs)
+        out["quartz/grid"] = {"f": pq.promolecular_grid((13, 11, 4 * (ndev + 1) + 2))}
+        o, xq, nq = drivers.cube_grid(q, (12, 10, 4 * ndev + 3))
+        out["quartz/cube"] = pq.cube(o, xq, nq, periodic=True)
+        return out
+
+    try:
+        G.init_devices([0])
+        one = run_all()
+        assert G.init(0) == ndev
+        many = run_all()
+    finally:
+        G.init_devices([0])
+    for key, d1 in one.items():
+        for name, a in d1.items():
+            assert np.array_equal(a, many[key][name]), f"{key}/{name} differs between 1 and {ndev} devices"

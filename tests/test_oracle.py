@@ -429,3 +429,34 @@ def test_nciplot_formulas_on_a_single_gaussian():
     r0 = ((x0 - st.r[0]) ** 2).sum()
     rho0 = 2 * c * c * np.exp(-2 * a * r0)
     np.testing.assert_allclose(ev, sorted([-4 * a * rho0, -4 * a * rho0, (16 * a * a * r0 - 4 * a) * rho0]), rtol=1e-10)
+
+
+def test_promolecular_grid_fragment_and_pair_count_against_brute_force():
+    """promolecular_grid's `fr` argument (crystalmod@proc.f90:5118-5158): fragment + complement = whole cell; the pair count
+    the roofline of the promolecular kernel is built on equals a brute-force count over the environment images."""
+    from critic2_b200 import drivers
+    from critic2_b200.structure import CUTRAD
+    st = cases.quartz(1)
+    tabs = cases.tables()
+    env = oracle.Environ(st)
+    grids = oracle.Grid1Set(tabs)
+    n = (9, 8, 7)
+    full = oracle.promolecular_grid(env, grids, n)
+    m = np.zeros(st.ncell, np.uint8)
+    m[[0, 3, 4]] = 1
+    a = oracle.promolecular_grid(env, grids, n, fragmask=m)
+    b = oracle.promolecular_grid(env, grids, n, fragmask=1 - m)
+    assert np.abs(a + b - full).max() <= 1e-14 * full.max() and 0 < a.max() < full.max()
+    o, xq, nq = drivers.cube_grid(st, (5, 4, 3))
+    I, J, K = np.meshgrid(*[np.arange(int(k)) for k in nq], indexing="ij")
+    pts = np.asarray(o)[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ np.asarray(xq).T
+    nat = oracle.promol_nat_points(env, grids, pts)
+    renv, cidx = st.environment_atoms()
+    zspc, iss = st.species()
+    z = zspc[iss[cidx - 1] - 1]
+    cut = np.array([min(CUTRAD[int(zz) - 1], tabs[int(zz)]["r"][-1]) for zz in z])
+    xr = (np.linalg.inv(st.m_xr2c) @ pts.T).T
+    xr -= np.floor(xr)
+    pc = (st.m_xr2c @ xr.T).T
+    d = np.linalg.norm(pc[:, None, :] - renv[None, :, :], axis=2)
+    assert np.array_equal(nat, (d <= cut[None, :]).sum(1))
