@@ -821,3 +821,25 @@ def test_multi_device_host_path_matches_one_device(G):
     for key, d1 in one.items():
         for name, a in d1.items():
             assert np.array_equal(a, many[key][name]), f"{key}/{name} differs between 1 and {ndev} devices"
+
+
+def test_libxc_reference_energies_through_the_point_list_path(G, O):
+    """The reference-held numbers of /root/reference/tests_libxc/ref.txt:1-2 (LDA and PBE energies of h2o.wfx on critic2's
+    default molecular mesh; see tests/test_oracle.py::test_libxc_reference_energies_pin_rho2) from the GPU's own rho and
+    |grad rho|: c2gpu_eval_points on the 52 246 mesh nodes (mesh%fill's point list, meshmod@proc.f90:446-470)."""
+    from oracle import mesh
+    from test_oracle import LIBXC_REF, LIBXC_TOL, _libxc_mesh_integrals
+    f = cases.golden_wfn("h2o-wfx")
+    st = cases.mol_structure(f)
+    x, w = mesh.genmesh_franchini(st.r, f.z)
+    res = G.WfnField(f, st).points(x, nder=1, periodic=True)
+    got = _libxc_mesh_integrals(res[:, 0], res[:, 13], w)
+    assert abs(got["nelec"] - 10.0) < 1e-5
+    assert abs(got["lda"] - LIBXC_REF["lda"]) < LIBXC_TOL and abs(got["pbe"] - LIBXC_REF["pbe"]) < LIBXC_TOL, got
+    ref = _ofield(O, f, st).grd_points(x, nder=1, periodic=True)
+    exp = _libxc_mesh_integrals(ref[:, 0], ref[:, 13], w)
+    for k in exp:
+        assert abs(got[k] - exp[k]) <= 1e-11 * abs(exp[k]), (k, got[k], exp[k])
+    check_rho(res[:, 0], ref[:, 0])
+    check_vec(res[:, 13:14], ref[:, 13:14], "gmod", rho=ref[:, 0])
+    print(got)

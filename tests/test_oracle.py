@@ -460,3 +460,59 @@ def test_promolecular_grid_fragment_and_pair_count_against_brute_force():
     pc = (st.m_xr2c @ xr.T).T
     d = np.linalg.norm(pc[:, None, :] - renv[None, :, :], axis=2)
     assert np.array_equal(nat, (d <= cut[None, :]).sum(1))
+
+
+# ---- the reference-held pin: /root/reference/tests_libxc/ref.txt:1-2 ----------------------------------------------------
+# LDA (SVWN) and PBE exchange-correlation energies of tests_libxc/h2o.wfx as the reference's own MOLCALC prints them
+# (tests_libxc/h2o.cri:4-5: molcalc "xc($1,1)+xc($1,8)", "xc($1,$1:g,101)+xc($1,$1:g,130)"): integrals over critic2's
+# default molecular mesh (Franchini, level good) of closed-form functionals of rho2's rho and |grad rho|.
+LIBXC_REF = {"lda": -8.957976118600001, "pbe": -9.242634846200005}
+# Agreement reached with the restated mesh: LDA +5.2e-6, PBE -9.9e-6 Ha (6 significant digits).  That is the mesh's own
+# resolution -- the same mesh integrates rho to 9.999994 electrons and its levels 2..5 scatter by +-1e-5 Ha around these
+# values -- so the remaining difference is a mesh-table detail of the critic2 build that wrote ref.txt (the Lebedev
+# submodule is not in the snapshot), not rho2.  A relative error of 2e-6 in rho or |grad rho| anywhere would break the test.
+LIBXC_TOL = 2e-5
+
+
+def _libxc_mesh_integrals(rho, gmod, w):
+    from oracle import xcfun
+    return {"nelec": float((rho * w).sum()),
+            "lda": float(((xcfun.xc(rho, ident=1) + xcfun.xc(rho, ident=8)) * w).sum()),
+            "pbe": float(((xcfun.xc(rho, gmod, 101) + xcfun.xc(rho, gmod, 130)) * w).sum())}
+
+
+def test_franchini_mesh_restatement():
+    from oracle import mesh
+    assert (mesh.z2nr(1, 3), mesh.z2nr(8, 3), mesh.z2nr(14, 3), mesh.z2nang(8, 3)) == (52, 69, 86, 302)
+    x, w = mesh.gauleg(-1.0, 1.0, 69)
+    xr, wr = np.polynomial.legendre.leggauss(69)
+    assert np.abs(x - xr).max() < 1e-14 and np.abs(w - wr).max() < 1e-14
+    # one hydrogen-like density exp(-2r)/pi integrates to 1 on a one-atom mesh; the Lebedev weights are normalised
+    ang, wang = mesh.lebedev(302)
+    assert abs(wang.sum() - 1.0) < 1e-14 and np.abs(np.linalg.norm(ang, axis=1) - 1.0).max() < 1e-14
+    xm, wm = mesh.genmesh_franchini(np.zeros((1, 3)), np.array([8]))
+    assert xm.shape == (69 * 302, 3)
+    r = np.linalg.norm(xm, axis=1)
+    assert abs((np.exp(-2.0 * r) / np.pi * wm).sum() - 1.0) < 1e-9
+    # two atoms: the Franchini weights partition space (a smooth function integrates to the same value as on one centre)
+    g = lambda p: np.exp(-0.7 * ((p - np.array([0.4, 0.1, -0.2])) ** 2).sum(1))
+    exact = (np.pi / 0.7) ** 1.5
+    x2, w2 = mesh.genmesh_franchini(np.array([[0.0, 0, 0], [1.8, 0, 0]]), np.array([8, 1]))
+    assert abs((g(x2) * w2).sum() - exact) < 2e-4 * exact
+
+
+def test_libxc_reference_energies_pin_rho2():
+    """The oracle's rho2 (rho, |grad rho| through grd) against the reference's own numbers."""
+    from oracle import mesh
+    f = cases.golden_wfn("h2o-wfx")               # = read_wfx(/root/reference/tests_libxc/h2o.wfx), tools/make_golden.py
+    st = cases.mol_structure(f)
+    x, w = mesh.genmesh_franchini(st.r, f.z)
+    assert len(w) == 69 * 302 + 2 * 52 * 302
+    res = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f)).grd_points(x, nder=1, periodic=True)
+    got = _libxc_mesh_integrals(res[:, 0], res[:, 13], w)
+    assert abs(got["nelec"] - 10.0) < 1e-5                         # molcalc_nelec, molcalc@proc.F90:80-103
+    assert abs(got["lda"] - LIBXC_REF["lda"]) < LIBXC_TOL, got
+    assert abs(got["pbe"] - LIBXC_REF["pbe"]) < LIBXC_TOL, got
+    # the pin discriminates: rho scaled by 1 + 3e-6 moves the LDA energy out of tolerance
+    bad = _libxc_mesh_integrals(res[:, 0] * (1 + 3e-6), res[:, 13], w)
+    assert abs(bad["lda"] - LIBXC_REF["lda"]) > LIBXC_TOL
