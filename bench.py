@@ -16,6 +16,9 @@ no data-path collective; the gather to the writer rank is part of the e2e leg on
              peak measured on this pool's B200 (profiles/r1_fp64_peak_microbench.log: MEASURED_PEAKS.json has no FP64).
 `cpu_baseline` / --impl reference: the CPU oracle (C + OpenMP restatement of the reference path; the Fortran reference
              cannot be built: no Fortran compiler) on a bounded sub-lattice of the same grid, all host cores.
+`parity`   : the e2e result at the CPU sample's points against the oracle's values (rho <= 1e-10, derivatives <= 1e-8 of
+             the vector / tensor norm, identical exact-zero masks); the run FAILS (exit 1) when it is violated.
+`aux`      : BASELINE configs 1, 2, 3 (N = 1) and 5 (N = 8) with their own roofline, cpu_baseline and parity blocks.
 """
 import argparse
 import json
@@ -32,6 +35,13 @@ sys.path.insert(0, ROOT)
 
 FP64_PEAK_TFLOPS = 37.1   # mma.sync m8n8k4 f64 chains, profiles/r1_fp64_peak_microbench.log (DFMA chains: 34.0)
 PROPS10 = ("f", "gx", "gy", "gz", "hxx", "hxy", "hxz", "hyy", "hyz", "hzz")
+TOL_RHO, TOL_DER = 1e-10, 1e-8     # BASELINE.json north_star
+
+
+def workload_name(n):
+    """config.workload of BOTH arms (the driver compares the strings)"""
+    return (f"cfg4: synthetic C160N20O20H300 (seed 4), def2-TZVP-shaped 12600 primitives, 780 MOs, rho+grad+Hessian "
+            f"(10 outputs/point), {n}^3 grid")
 
 
 def parse():
@@ -46,8 +56,11 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-stride", type=int, default=8, help="sub-lattice stride of the CPU sample")
     ap.add_argument("--aux", default="", choices=["", "configs", "format"],
-                    help="secondary measurements with their CPU baselines: BASELINE configs 1,2,3,5 (tools/bench_configs.py) "
-                         "or the cube-text formatter (tools/bench_format.py); extra arguments go to the tool")
+                    help="run ONLY a secondary measurement with its CPU baselines: BASELINE configs 1,2,3,5 "
+                         "(tools/bench_configs.py) or the cube-text formatter (tools/bench_format.py); extra arguments go to the tool")
+    ap.add_argument("--no-aux", action="store_true", help="skip the aux entries (configs 1,2,3 at N=1; 5 at N=8) of the line")
+    ap.add_argument("--aux-cfg5", action="store_true", help="run the config-5 aux entry at any N (default: N = 8 only)")
+    ap.add_argument("--e2e-calls", type=int, default=3, help="timed end-to-end calls (after one warm-up call)")
     return ap.parse_known_args()
 
 
@@ -102,13 +115,21 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def sample_index(nn, stride):
+    """flat x-fastest indices and (i, j, k) of the sub-lattice (stride // 2 + stride * m) of an nn grid"""
+    idx = [np.arange(stride // 2, int(n), stride) for n in nn]
+    I, J, K = np.meshgrid(*idx, indexing="ij")
+    ijk = np.stack([I.ravel(), J.ravel(), K.ravel()], 1)
+    flat = ijk[:, 0] + int(nn[0]) * (ijk[:, 1] + int(nn[1]) * ijk[:, 2])
+    return flat, ijk
+
+
 def cpu_sample(f, st, lo, xd, nn, stride, reps=1):
     """The CPU oracle (OpenMP, all cores) on the sub-lattice (stride,stride,stride) of the workload grid, nder = 2."""
     import oracle
     oracle.build()
-    idx = [np.arange(stride // 2, int(n), stride) for n in nn]
-    I, J, K = np.meshgrid(*idx, indexing="ij")
-    pts = lo[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ xd.T
+    _, ijk = sample_index(nn, stride)
+    pts = lo[None, :] + ijk.astype(float) @ xd.T
     fld = oracle.Field(oracle.Environ(st), wfn=oracle.Wfn(f))
     cores = os.cpu_count() or 1
     t0 = time.perf_counter()
@@ -118,9 +139,42 @@ def cpu_sample(f, st, lo, xd, nn, stride, reps=1):
     return pts, res, dt, cores
 
 
+# ---- parity blocks -------------------------------------------------------------------------------------------------------
+def _vec_err(got, ref, rho):
+    """max over points of |got - ref| / max(|ref vector|, 1e-4 rho): the measure of tests/cases.py check_vec"""
+    nrm = np.sqrt((ref ** 2).sum(-1))
+    floor = np.maximum(1e-4 * np.abs(rho), 1e-20)
+    return float((np.abs(got - ref).max(-1) / np.maximum(nrm, floor)).max())
+
+
+def parity_fields(rho, rho_ref, vecs, sample):
+    """rho: (n,), vecs: [(name, got (n,k), ref (n,k))] -> the `parity` object of a bench line"""
+    rho, rho_ref = np.asarray(rho), np.asarray(rho_ref)
+    zero_eq = bool(np.array_equal(rho == 0.0, rho_ref == 0.0))
+    e_rho = float((np.abs(rho - rho_ref) / np.maximum(np.abs(rho_ref), 1e-30)).max())
+    out = {"points": int(rho.size), "sample": sample, "rho_max_rel": e_rho, "zero_mask_equal": zero_eq,
+           "nonzero_points": int(np.count_nonzero(rho_ref))}
+    worst = 0.0
+    for name, got, ref in vecs:
+        e = _vec_err(np.asarray(got), np.asarray(ref), rho_ref)
+        out[f"{name}_max_rel"] = e
+        worst = max(worst, e)
+    out["deriv_max_rel"] = worst
+    out["tol"] = {"rho": TOL_RHO, "deriv": TOL_DER}
+    out["ok"] = bool(zero_eq and e_rho <= TOL_RHO and worst <= TOL_DER)
+    return out
+
+
+def parity_cube10(vals, res, sample):
+    """vals: (n, 10) GPU f, g(3), h(xx,xy,xz,yy,yz,zz); res: oracle grd rows (f, gf(3), hf(3,3), ...)"""
+    hcols = [4, 5, 6, 8, 9, 12]
+    return parity_fields(vals[:, 0], res[:, 0], [("grad", vals[:, 1:4], res[:, 1:4]), ("hess", vals[:, 4:10], res[:, hcols])],
+                         sample)
+
+
 class CpuLegs:
-    """CPU baselines of the secondary measurements (--aux): the oracle on all host cores, bounded samples.  bench.py is
-    the only non-test code that runs the oracle; tools/bench_*.py receive this object and never import it."""
+    """CPU baselines and parity checks of the secondary measurements: the oracle on all host cores, bounded samples.
+    bench.py is the only non-test code that runs the oracle; tools/bench_*.py receive this object and never import it."""
 
     def __init__(self):
         import oracle
@@ -131,32 +185,87 @@ class CpuLegs:
     def _res(self, npts, dt, sample):
         return {"value": npts / dt, "unit": "points/s", "cores": self.cores, "kind": "port", "sample": sample}
 
-    def cube(self, f, st, x0, xd, nn, props):
+    def cube(self, f, st, x0, xd, nn, props, got=None):
+        """full-grid CUBE on the CPU; got: {prop: GPU array} -> (cpu_baseline, parity)"""
         fld = self.o.Field(self.o.Environ(st), wfn=self.o.Wfn(f))
         t0 = time.perf_counter()
-        fld.cube(x0, xd, nn, props=tuple(props), periodic=False, nthreads=self.cores)
-        return self._res(int(np.prod(nn)), time.perf_counter() - t0, "full grid, one nder=2 evaluation per point")
+        ref = fld.cube(x0, xd, nn, periodic=False, nthreads=self.cores)          # all 12 properties of one nder=2 pass
+        base = self._res(int(np.prod(nn)), time.perf_counter() - t0, "full grid, one nder=2 evaluation per point")
+        par = None
+        if got is not None:
+            r = {k: v.reshape(-1) for k, v in ref.items()}
+            g = {k: np.asarray(v).reshape(-1) for k, v in got.items()}
+            hk = ("hxx", "hxy", "hxz", "hyy", "hyz", "hzz")
+            hn = np.sqrt(sum(r[k] ** 2 for k in hk))
+            par = parity_fields(g["f"], r["f"], [("grad", np.stack([g[k] for k in ("gx", "gy", "gz")], -1),
+                                                  np.stack([r[k] for k in ("gx", "gy", "gz")], -1))], "every point of the grid")
+            e_lap = float((np.abs(g["lap"] - r["lap"]) / np.maximum(np.maximum(hn, 1e-4 * np.abs(r["f"])), 1e-20)).max())
+            par["lap_max_rel_of_hessian_norm"] = e_lap
+            par["deriv_max_rel"] = max(par["deriv_max_rel"], e_lap)
+            par["ok"] = bool(par["ok"] and e_lap <= TOL_DER)
+        return base, par
 
-    def nci(self, f, st, x0, xmat, ns):
-        fld = self.o.Field(self.o.Environ(st), wfn=self.o.Wfn(f))
-        sub = np.array([max(1, int(ns[0]) // 8), int(ns[1]), int(ns[2])], np.int32)     # every 8th x-plane
-        xm = np.array(xmat, float).copy()
-        xm[:, 0] *= float(ns[0]) / float(sub[0])
+    def nci_parity(self, f, st, x0, xmat, ns, got, got_masked, got_sums, got_ndat, rho_void, sample,
+                   rhocut=0.2, dimcut=2.0, rhoplot=0.1):
+        """NCIPLOT on the (sub-)lattice x0, xmat, ns on the CPU against the GPU's values there.  got: [crho, cgrad, rhoat or
+        None] (flat, z fastest) BEFORE the cutoff pass; got_masked / got_sums / got_ndat: what the GPU cutoff pass made of
+        them.  Classification = .dat membership count, the cgrad = 100 mask and sign(lambda2)."""
+        o = self.o
+        env = o.Environ(st)
+        fld = o.Field(env, wfn=o.Wfn(f))
+        pro = o.Field(env, grids=o.Grid1Set(_tables())) if got[2] is not None else None
         t0 = time.perf_counter()
-        fld.nci(x0, xm, sub, nthreads=self.cores)
-        return self._res(int(np.prod(sub)), time.perf_counter() - t0, f"{sub[0]} of {int(ns[0])} x-planes, NCIPLOT evaluation loop")
+        rrho, rgrad, rat = fld.nci(x0, xmat, ns, promol=pro, nthreads=self.cores)
+        base = self._res(int(np.prod(ns)), time.perf_counter() - t0, sample + ", NCIPLOT evaluation loop")
+        rrho, rgrad = rrho.reshape(-1), rgrad.reshape(-1)
+        crho, cgrad = np.asarray(got[0]).reshape(-1), np.asarray(got[1]).reshape(-1)
+        rho = np.maximum(np.abs(rrho) / 100.0, 1e-80)
+        floor = 1e-4 * rho / (2.0 * (3.0 * np.pi ** 2) ** (1.0 / 3.0) * rho ** (4.0 / 3.0))
+        big = rgrad < 1e40
+        par = {"points": int(rrho.size), "sample": sample,
+               "rho_max_rel": float((np.abs(np.abs(crho) - np.abs(rrho)) / np.maximum(np.abs(rrho), 1e-30)).max()),
+               "zero_mask_equal": bool(np.array_equal(crho == 0.0, rrho == 0.0)),
+               "rdg_max_rel": float((np.abs(cgrad - rgrad) / np.maximum(np.abs(rgrad), floor))[big].max()),
+               "sign_lambda2_flips": int(np.count_nonzero(np.sign(crho) != np.sign(rrho)))}
+        ok = par["zero_mask_equal"] and par["rho_max_rel"] <= TOL_RHO and par["rdg_max_rel"] <= TOL_DER and \
+            par["sign_lambda2_flips"] == 0
+        if rat is not None:
+            cat = np.asarray(got[2]).reshape(-1)
+            rat = rat.reshape(-1)
+            par["rhoat_max_rel"] = float((np.abs(cat - rat) / np.maximum(np.abs(rat), 1e-30)).max())
+            ok = ok and par["rhoat_max_rel"] <= TOL_RHO and bool(np.array_equal(cat == 0.0, rat == 0.0))
+        rg = rgrad.copy().reshape(tuple(int(v) for v in ns))
+        rsums, rdat = o.nci_cutoffs(rrho.copy().reshape(rg.shape), rg, None if rat is None else rat.reshape(rg.shape),
+                                    rhocut=rhocut, dimcut=dimcut, rhoplot=rhoplot, rho_void=rho_void, omega=float(rrho.size))
+        par["dat_count"] = [int(got_ndat), int(len(rdat))]
+        par["masked_points"] = [int(np.count_nonzero(np.asarray(got_masked) == 100.0)), int(np.count_nonzero(rg == 100.0))]
+        par["classification_identical"] = bool(got_ndat == len(rdat) and
+                                               np.array_equal(np.asarray(got_masked).reshape(-1) == 100.0, rg.reshape(-1) == 100.0))
+        if rho_void > 0:      # oracle sums carry omega / npts = 1 here: raw sums on both sides
+            par["void_sums_max_rel"] = float((np.abs(np.asarray(got_sums) - rsums) / np.maximum(np.abs(rsums), 1e-300)).max())
+            ok = ok and par["void_sums_max_rel"] <= TOL_RHO
+        par["deriv_max_rel"] = par["rdg_max_rel"]
+        par["tol"] = {"rho": TOL_RHO, "deriv": TOL_DER}
+        par["ok"] = bool(ok and par["classification_identical"])
+        return par, base
 
-    def promol(self, st, tables, x0, xd, nn, nder):
+    def promol(self, st, tables, x0, xd, nn, nder, got=None, zstride=16):
+        """every zstride-th z-plane on the CPU; got: callable(flat indices) -> (n, 1 or 10) GPU values there"""
         fld = self.o.Field(self.o.Environ(st), grids=self.o.Grid1Set(tables))
-        sub = np.array([int(nn[0]), int(nn[1]), max(1, int(nn[2]) // 16)], np.int32)  # every 16th z-plane
-        xs = np.array(xd, float).copy()
-        xs[:, 2] *= float(nn[2]) / float(sub[2])
-        idx = [np.arange(int(n)) for n in sub]
-        I, J, K = np.meshgrid(*idx, indexing="ij")
-        pts = np.asarray(x0, float)[None, :] + np.stack([I.ravel(), J.ravel(), K.ravel()], 1).astype(float) @ xs.T
+        kz = np.arange(0, int(nn[2]), zstride)
+        I, J, K = np.meshgrid(np.arange(int(nn[0])), np.arange(int(nn[1])), kz, indexing="ij")
+        ijk = np.stack([I.ravel(), J.ravel(), K.ravel()], 1)
+        pts = np.asarray(x0, float)[None, :] + ijk.astype(float) @ np.asarray(xd, float).T
         t0 = time.perf_counter()
-        fld.grd_points(pts, nder=nder, periodic=True, nthreads=self.cores)
-        return self._res(len(pts), time.perf_counter() - t0, f"{sub[2]} of {int(nn[2])} z-planes, nder={nder}")
+        res = fld.grd_points(pts, nder=nder, periodic=True, nthreads=self.cores)
+        sample = f"{len(kz)} of {int(nn[2])} z-planes, nder={nder}"
+        base = self._res(len(pts), time.perf_counter() - t0, sample)
+        par = None
+        if got is not None:
+            flat = ijk[:, 0] + int(nn[0]) * (ijk[:, 1] + int(nn[1]) * ijk[:, 2])
+            vals = got(flat)
+            par = parity_cube10(vals, res, sample) if nder == 2 else parity_fields(vals[:, 0], res[:, 0], [], sample)
+        return base, par
 
     def text(self, sample, fmt):
         t0 = time.perf_counter()
@@ -165,12 +274,19 @@ class CpuLegs:
                 "sample": f"{sample.shape[0]}^3 values, C oracle (glibc %.*E, OpenMP)"}
 
 
+def _tables():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import cases
+    return cases.tables()
+
+
 def run_aux(a, rest):
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     cpu = None if a.no_cpu else CpuLegs()
     if a.aux == "configs":
         import bench_configs
-        bench_configs.main(rest, cpu)
+        for d in bench_configs.main(rest, cpu):
+            print(json.dumps(d), flush=True)
     else:
         import bench_format
         bench_format.main(rest, cpu)
@@ -196,8 +312,7 @@ def run_reference(a):
     line = {"impl": "reference", "metric": "grid points/sec (rho+grad+Hessian)", "value": v, "unit": "points/s",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": tot / a.steps * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"cfg4: synthetic C160N20O20H300, 12600 primitives, 780 MOs, rho+grad+Hessian, {a.n}^3 grid",
-                       "sampled": sample},
+            "config": {"workload": workload_name(a.n), "sampled": sample},
             "cpu_baseline": {"value": v, "unit": "points/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -207,7 +322,7 @@ def run_reference(a):
 def run_ours(a):
     import torch
     import torch.distributed as dist
-    from critic2_b200 import gpu
+    from critic2_b200 import gpu, sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -215,14 +330,16 @@ def run_ours(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the hot path has no CPU fallback")
     torch.cuda.set_device(local)
+    shared = None
     if world > 1:
-        # rank 0 prints exactly one JSON line on stdout: NCCL's log (its version banner is printed from level VERSION up,
-        # WARN included) goes to stderr
-        os.environ["NCCL_DEBUG"] = "WARN"
-        os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+        # rank 0 prints exactly one JSON line on stdout; NCCL's log (whatever level the caller asked for) goes to stderr
+        os.environ.setdefault("NCCL_DEBUG", "WARN")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        shared = sharding.SharedPinned(rank, world, dist)
     gpu.init_devices([local])
     dev = torch.device("cuda", local)
+    peak_now = gpu.fp64_peak() if rank == 0 else None       # (DMMA, DFMA) TFLOP/s measured on this GPU, now
 
     f, st, lo, xd, nn = workload(a.n)
     if a.cfg >= 0:
@@ -248,10 +365,6 @@ def run_ours(a):
         nact, mypts = float(tt[0].item()) / world, float(tt[1].item()) / world
     flops = 2.0 * 10 * nact * f.nmoocc + 80.0 * nact + 60.0 * f.nmoocc * mypts
 
-    def step():
-        flush.zero_()
-        fld.cube_dev_part(lo, xd, nn, outs, PROPS10, rank, world, stream=stream, rows=world > 1)
-
     def sync():
         torch.cuda.synchronize()
         if world > 1:
@@ -259,7 +372,8 @@ def run_ours(a):
             torch.cuda.synchronize()
 
     for _ in range(a.warmup):
-        step()
+        flush.zero_()
+        fld.cube_dev_part(lo, xd, nn, outs, PROPS10, rank, world, stream=stream, rows=world > 1)
     sync()
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = gpu.launch_count()
@@ -282,75 +396,163 @@ def run_ours(a):
     ms_total = float(ms.item())
     value = npts_total * a.steps / (ms_total * 1e-3)
 
-    # ---- e2e through the C-ABI host entry (rank-local share at N>1, then NCCL reduce to the writer rank) ----------
-    e2e = None
+    # ---- e2e: results in HOST memory.  N = 1: the C-ABI host entry c2gpu_eval_grid (host descriptors in, fresh pageable
+    # host arrays out).  N > 1 (one process per GPU): c2gpu_eval_grid_dev_part_rows + c2gpu_gather_part_host, every rank
+    # copying the rows it owns over its own PCIe link into ONE shared page-locked host buffer (the writer rank's arrays) --
+    # no inter-GPU traffic, 1/N of the bytes per link. ----------------------------------------------------------------------
+    e2e, host_vals, e2e_sp = None, None, None
+    flat_idx, _ = sample_index(nn, a.cpu_stride)
     if not a.no_e2e:
+        tes = []
         if world == 1:
-            host = fld.cube(lo, xd, nn, props=PROPS10)     # warm-up call (device output arrays are kept by the handle)
-            del host
-            t0 = time.perf_counter()
-            host = fld.cube(lo, xd, nn, props=PROPS10)
-            te = time.perf_counter() - t0
-            d2h = sum(v.nbytes for v in host.values())
-            chk = float(host["f"].sum())
-            del host
+            for it in range(1 + a.e2e_calls):               # first call = warm-up (device output arrays kept by the handle)
+                t0 = time.perf_counter()
+                host = fld.cube(lo, xd, nn, props=PROPS10)
+                if it > 0:
+                    tes.append(time.perf_counter() - t0)
+                d2h = sum(v.nbytes for v in host.values())
+                if it == a.e2e_calls:
+                    chk = float(host["f"].sum())
+                    host_vals = np.stack([host[p].reshape(-1)[flat_idx] for p in PROPS10], 1)
+                del host
+            note = ("field handle (LOAD) resident; inputs per step are the grid descriptor; outputs to fresh pageable host "
+                    f"arrays; mean of {a.e2e_calls} calls after one warm-up call")
         else:
-            pin = torch.empty(npts_total, dtype=torch.float64).pin_memory() if rank == 0 else None
-            for o in outs:
-                o.zero_()
-            sync()
-            t0 = time.perf_counter()
-            fld.cube_dev_part(lo, xd, nn, outs, PROPS10, rank, world, stream=stream, rows=True)
-            d2h = 0
-            for o in outs:   # layers are disjoint across ranks: a sum-reduce to the writer rank is an exact gather
-                dist.reduce(o, dst=0, op=dist.ReduceOp.SUM)
-                if rank == 0:
-                    pin.copy_(o)
-                    d2h += pin.numel() * 8
-            torch.cuda.synchronize()
-            dist.barrier()
-            te = time.perf_counter() - t0
-            chk = float(outs[0].sum().item())
-        tt = torch.tensor([te], dtype=torch.float64, device=dev)
+            hbuf = shared.get(len(PROPS10) * npts_total * 8, "cfg4")
+            hptr = [hbuf.ctypes.data + k * npts_total * 8 for k in range(len(PROPS10))]
+            d2h = len(PROPS10) * npts_total * 8
+            for it in range(1 + a.e2e_calls):
+                sync()
+                t0 = time.perf_counter()
+                fld.cube_dev_part(lo, xd, nn, outs, PROPS10, rank, world, stream=stream, rows=True)
+                fld.gather_part_host(nn, outs, hptr, rank, world, rows=True, stream=stream)
+                dist.barrier()
+                if it > 0:
+                    tes.append(time.perf_counter() - t0)
+            hv = hbuf.reshape(len(PROPS10), npts_total)
+            if rank == 0:
+                chk = float(hv[0].sum())
+                host_vals = np.stack([hv[k][flat_idx] for k in range(len(PROPS10))], 1)
+            note = (f"per-rank rows of super-tiles + c2gpu_gather_part_host into one shared page-locked host buffer ({world} "
+                    f"PCIe links in parallel, no inter-GPU traffic); mean of {a.e2e_calls} steps after one warm-up step")
+        tt = torch.tensor([float(np.mean(tes)), float(np.min(tes)), float(np.max(tes))], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e = {"value": npts_total / float(tt.item()), "unit": "points/s", "h2d_bytes_per_step": 3 * 8 + 9 * 8 + 3 * 4,
-               "d2h_bytes_per_step": int(d2h), "ms": float(tt.item()) * 1e3, "checksum_rho": chk,
-               "note": "field handle (LOAD) resident; inputs per step are the grid descriptor; outputs to fresh pageable host arrays; one warm-up call"
-                       if world == 1 else "per-rank layers + NCCL reduce to rank 0 + D2H to pinned host on rank 0"}
+        if rank == 0:
+            e2e = {"value": npts_total / float(tt[0].item()), "unit": "points/s", "h2d_bytes_per_step": 3 * 8 + 9 * 8 + 3 * 4,
+                   "d2h_bytes_per_step": int(d2h), "ms": float(tt[0].item()) * 1e3, "ms_min": float(tt[1].item()) * 1e3,
+                   "ms_max": float(tt[2].item()) * 1e3, "calls": a.e2e_calls, "checksum_rho": chk, "note": note}
 
-    cpu = None
+        # ---- the same pass through the single-process host entry over all N devices (what the Fortran caller gets from
+        # gpu_init -> c2gpu_init(0)): rank 0 alone drives every GPU, the other ranks wait on the host ------------------------
+        if world > 1:
+            outs = None
+            torch.cuda.empty_cache()
+            store = dist.distributed_c10d._get_default_store()
+            sync()
+            if rank == 0:
+                try:
+                    gpu.init(world)
+                    fsp = gpu.WfnField(f, st)
+                    tsp = []
+                    for it in range(1 + a.e2e_calls):
+                        t0 = time.perf_counter()
+                        host = fsp.cube(lo, xd, nn, props=PROPS10)
+                        if it > 0:
+                            tsp.append(time.perf_counter() - t0)
+                        same = bool(np.array_equal(np.stack([host[p].reshape(-1)[flat_idx] for p in PROPS10], 1), host_vals))
+                        del host
+                    e2e_sp = {"value": npts_total / float(np.mean(tsp)), "unit": "points/s", "ms": float(np.mean(tsp)) * 1e3,
+                              "ms_min": float(np.min(tsp)) * 1e3, "calls": a.e2e_calls, "devices": world,
+                              "equals_per_process_result_at_sample": same,
+                              "note": "c2gpu_init(N) + c2gpu_eval_grid from ONE process over all N devices, pageable host "
+                                      "arrays out; the other ranks idle"}
+                    fsp.close()
+                except Exception as ex:      # reported, not fatal: the headline numbers stand
+                    e2e_sp = {"error": str(ex)}
+                finally:
+                    gpu.init_devices([local])
+                    store.set("c2gpu_sp_done", "1")
+            else:
+                import datetime
+                store.wait(["c2gpu_sp_done"], datetime.timedelta(minutes=20))
+
+    cpu, parity = None, None
     if rank == 0 and not a.no_cpu:
-        pts, _, dt, cores = cpu_sample(f, st, lo, xd, nn, a.cpu_stride)
-        cpu = {"value": len(pts) / dt, "unit": "points/s", "cores": cores, "kind": "port",
-               "sample": f"sub-lattice stride {a.cpu_stride} of the {a.n}^3 grid ({len(pts)} points, {dt:.1f} s), nder=2"}
+        pts, res, dt, cores = cpu_sample(f, st, lo, xd, nn, a.cpu_stride)
+        sample = f"sub-lattice stride {a.cpu_stride} of the {a.n}^3 grid ({len(pts)} points, {dt:.1f} s), nder=2"
+        cpu = {"value": len(pts) / dt, "unit": "points/s", "cores": cores, "kind": "port", "sample": sample}
+        if host_vals is None and world == 1:     # --no-e2e: the device-resident arrays of the timed region
+            idx = torch.from_numpy(flat_idx).to(dev)
+            host_vals = torch.stack([o.index_select(0, idx) for o in outs], 1).cpu().numpy()
+        if host_vals is not None:
+            parity = parity_cube10(host_vals, res, sample)
+            parity["source"] = "e2e host arrays" if e2e else "device arrays of the timed region"
 
+    # ---- aux: the other BASELINE configs (1, 2, 3 on one GPU; 5 on eight) ------------------------------------------------
+    aux = []
+    if not a.no_aux:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        fld.close()
+        outs = flush = None
+        torch.cuda.empty_cache()
+        legs = CpuLegs() if (rank == 0 and not a.no_cpu) else None
+        if world == 1:
+            import bench_configs
+            aux += bench_configs.main(["--cfgs", "1,2,3"], legs)
+        if world == 8 or a.aux_cfg5:
+            import bench_cfg5
+            d5 = bench_cfg5.run(rank, world, dev, dist if world > 1 else None, steps=1, warmup=1, cpu=legs,
+                                shared_host=shared.get if shared else None)
+            if rank == 0:
+                aux.append(d5)
+
+    ok = True
     if rank == 0:
         ach = flops / (kms * 1e-3) / 1e12
         line = {"metric": "grid points/sec (rho+grad+Hessian)", "value": value, "unit": "points/s", "n_gpus": world,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"cfg4: synthetic C160N20O20H300 (seed 4), def2-TZVP-shaped 12600 primitives, 780 MOs, "
-                                       f"rho+grad+Hessian (10 outputs/point), {a.n}^3 grid",
+                "config": {"workload": workload_name(a.n),
                            "parallelism": (f"z-layers of {lh} planes on 1 GPU" if world == 1 else
                                            f"rows of super-tiles ({lh} planes x {lh} y-lines) round-robin over {world} GPUs"),
                            "l2": f"256 MiB flush write between steps; outputs {80.0 * npts_total / 1e9:.2f} GB/step vs 126 MB L2",
                            "kernel": cfg},
                 "roofline": {"bound": "tensor", "achieved": ach, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
                              "frac": ach / FP64_PEAK_TFLOPS,
-                             # dram__bytes_read.sum + dram__bytes_write.sum of one whole-grid launch on one GPU (ncu,
-                             # profiles/r1_ncu_dram_wfn_ws_kernel_400.txt): chi-tile cache spills, not algorithmic bytes
-                             "traffic": 1.026e13 if (a.n == 400 and world == 1 and cfg["cfg"] == 6) else None,
-                             "traffic_unit": "bytes/launch",
+                             "peak_measured_in_run": {"dmma_tflops": peak_now[0], "dfma_tflops": peak_now[1],
+                                                      "how": "c2gpu_fp64_peak: independent mma.sync m8n8k4 f64 / DFMA chains, "
+                                                             "best of 3, on this GPU before the timed region"},
+                             "traffic": TRAFFIC.get((a.n, world, cfg["cfg"])), "traffic_unit": "bytes/launch",
+                             "traffic_source": TRAFFIC_SOURCE if (a.n, world, cfg["cfg"]) in TRAFFIC else None,
                              "kernel": f"{'wfn_ws_kernel' if cfg['cfg'] == 6 else 'wfn_grid_kernel'} cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, "
                                        f"P={cfg['points_per_tile']}, NB={cfg['mo_block']})", "kernel_ms": kms,
                              "algorithmic_flops_per_launch": flops, "mean_n_act": nact / max(mypts, 1),
                              "peak_source": "measured FP64 mma.sync (DMMA) peak, profiles/r1_fp64_peak_microbench.log; "
                                             "MEASURED_PEAKS.json holds no FP64 figure"},
-                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+                "cpu_baseline": cpu, "parity": parity, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+        if e2e_sp is not None:
+            line["e2e_single_process"] = e2e_sp
+        if aux:
+            line["aux"] = aux
         print(json.dumps(line), flush=True)
+        bad = [("headline", parity)] + [(f"cfg{d.get('cfg')}", d.get("parity")) for d in aux]
+        for name, p in bad:
+            if p is not None and not p.get("ok", True):
+                ok = False
+                print(f"bench.py: PARITY FAILURE in {name}: {json.dumps(p)}", file=sys.stderr, flush=True)
+    if shared:
+        shared.close()
     if world > 1:
         dist.destroy_process_group()
+    if not ok:
+        raise SystemExit(1)
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE whole-grid launch on one GPU from an `ncu --set full` capture (not
+# measured in the run): keyed by (grid, n_gpus, kernel cfg); chi-tile cache spills, not algorithmic bytes
+TRAFFIC = {(400, 1, 6): 1.026e13}
+TRAFFIC_SOURCE = "ncu, profiles/r1_ncu_dram_wfn_ws_kernel_400.txt"
 
 
 if __name__ == "__main__":

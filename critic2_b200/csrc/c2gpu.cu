@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <numeric>
+#include <thread>
 
 #include "c2gpu_internal.h"
 
@@ -85,6 +86,10 @@ struct Replica {
   // scratch of the two-pass NCIPLOT evaluation: ten raw sums per point of the evaluated range, grow-only
   double *rawbuf = nullptr;
   size_t rawbuf_n = 0;
+  // copy-back of the host-array drivers: own copy stream, two pinned bounce buffers and their events (host_eval)
+  cudaStream_t cstream = nullptr;
+  char *bounce[2] = {nullptr, nullptr};
+  cudaEvent_t bev[2] = {nullptr, nullptr};
 };
 
 struct Handle {
@@ -179,6 +184,11 @@ int c2gpu_destroy(void *handle) {
     if (r.corebuf) cudaFree(r.corebuf);
     if (r.rawbuf) cudaFree(r.rawbuf);
     if (r.stream) cudaStreamDestroy(r.stream);
+    if (r.cstream) cudaStreamDestroy(r.cstream);
+    for (int b = 0; b < 2; b++) {
+      if (r.bounce[b]) cudaFreeHost(r.bounce[b]);
+      if (r.bev[b]) cudaEventDestroy(r.bev[b]);
+    }
   }
   delete h;
   return 0;

@@ -27,6 +27,7 @@ cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &x
                              cudaStream_t st);
 cudaError_t nci_epilogue_launch(const GridDesc &g, const OutDesc &o, const double *raw, size_t stride, double nci_const,
                                 cudaStream_t st);
+cudaError_t fp64_peak_measure(double *dmma_tflops, double *dfma_tflops);
 cudaError_t promol_launch(int nd, const PromolParams &p, int grid, cudaStream_t st);
 cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, int nfrag,
                                const double *rhofrag, double rhoparam, double rhoparam2, double rhocut,

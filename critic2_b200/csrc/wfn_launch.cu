@@ -212,6 +212,69 @@ cudaError_t nci_epilogue_launch(const GridDesc &g, const OutDesc &o, const doubl
   return cudaGetLastError();
 }
 
+// ---- diagnostic: FP64 peaks of this device, the roofline denominators of bench.py (the same chains as tools/fp64_peak.cu:
+// 16 independent m8n8k4 DMMA accumulator pairs / 16 independent DFMA chains per thread, 2 CTAs of 256 threads per SM) -------
+__global__ void __launch_bounds__(256) fp64_peak_dmma_kernel(double *out, int iters, double a, double b) {
+  double c[16][2];
+#pragma unroll
+  for (int i = 0; i < 16; i++) { c[i][0] = threadIdx.x; c[i][1] = i; }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) dmma884(c[i][0], c[i][1], a, b);
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 16; i++) s += c[i][0] + c[i][1];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) fp64_peak_dfma_kernel(double *out, int iters, double a, double b) {
+  double acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) acc[i] = threadIdx.x * 1e-3 + i;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] = fma(acc[i], a, b);
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < 16; i++) s += acc[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t fp64_peak_measure(double *dmma_tflops, double *dfma_tflops) {
+  int dev = 0, nsm = 0;
+  cudaGetDevice(&dev);
+  cudaError_t e = cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) return e;
+  const int grid = nsm * 2, iters = 20000;
+  double *out = nullptr;
+  if ((e = cudaMalloc(&out, sizeof(double) * 256 * (size_t)grid)) != cudaSuccess) return e;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best[2] = {1e30f, 1e30f};
+  for (int rep = 0; rep < 4; rep++)          // first repetition = warm-up
+    for (int k = 0; k < 2; k++) {
+      cudaEventRecord(e0);
+      if (k == 0) fp64_peak_dmma_kernel<<<grid, 256>>>(out, iters, 1.0000001, 1e-9);
+      else fp64_peak_dfma_kernel<<<grid, 256>>>(out, iters, 1.0000001, 1e-9);
+      g_launches++;
+      cudaEventRecord(e1);
+      if ((e = cudaEventSynchronize(e1)) != cudaSuccess) break;
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, e1);
+      if (rep > 0 && ms < best[k]) best[k] = ms;
+    }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  if (e != cudaSuccess) return e;
+  // one warp-level m8n8k4 DMMA = 2*8*8*4 flops -> 2*256*... per thread: 16 per lane
+  *dmma_tflops = 2.0 * 16 * 256 * (double)iters * 8.0 * grid / best[0] / 1e9;
+  *dfma_tflops = 2.0 * 16 * (double)iters * 256.0 * grid / best[1] / 1e9;
+  return cudaSuccess;
+}
+
 cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &xf, unsigned long long *count,
                              cudaStream_t st) {
   size_t ntot = (size_t)grid_na(g) * grid_nb(g) * (size_t)(g.c1 - g.c0);

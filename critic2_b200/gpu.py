@@ -57,6 +57,8 @@ def lib():
                                                C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_eval_grid_dev_part_rows.argtypes = L.c2gpu_eval_grid_dev_part.argtypes
         L.c2gpu_layer_height.argtypes = [C.c_void_p]
+        L.c2gpu_gather_part_host.argtypes = [C.c_void_p, ip, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                             C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_nci_grid_dev_part.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_nci_grid.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, dp, dp, dp]
@@ -94,6 +96,7 @@ def lib():
         L.c2gpu_wfn_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_int, dp]
         L.c2gpu_promol_count_active.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, dp]
         L.c2gpu_wfn_config.argtypes = [C.c_void_p, ip]
+        L.c2gpu_fp64_peak.argtypes = [dp, dp]
         _lib = L
     return _lib
 
@@ -142,6 +145,13 @@ def init_devices(devs) -> None:
 
 def set_option(name: str, value: int) -> None:
     _check(lib().c2gpu_set_option(name.encode(), int(value)))
+
+
+def fp64_peak():
+    """(DMMA TFLOP/s, DFMA TFLOP/s) of the first device, measured now."""
+    a, b = C.c_double(0), C.c_double(0)
+    _check(lib().c2gpu_fp64_peak(C.byref(a), C.byref(b)))
+    return a.value, b.value
 
 
 def launch_count() -> int:
@@ -212,6 +222,16 @@ class _Field:
 
     def layer_height(self) -> int:
         return int(lib().c2gpu_layer_height(self.handle))
+
+    def gather_part_host(self, nn, dev_arrays, host_ptrs, part: int, nparts: int, rows: bool = False,
+                         nci_order: bool = False, stream: int = 0):
+        """Copy the blocks `part` owns from full-size DEVICE tensors into full-size HOST arrays (addresses in host_ptrs;
+        one shared page-locked buffer when every rank passes the same memory): the gather to the writer rank."""
+        na = _i32(nn)
+        d = (C.c_void_p * len(dev_arrays))(*[C.c_void_p(t.data_ptr()) for t in dev_arrays])
+        hp = (C.c_void_p * len(host_ptrs))(*[C.c_void_p(int(p)) for p in host_ptrs])
+        _check(lib().c2gpu_gather_part_host(self.handle, _i(na), int(nci_order), len(dev_arrays), d, hp, part, nparts,
+                                            int(rows), C.c_void_p(stream)))
 
     # -- nciplot evaluation loop, nci@proc.f90:499-561 ----------------------------------------------------------
     def nci(self, x0, xmat, nstep, promol: "_Field | None" = None):

@@ -18,6 +18,8 @@ module gpu_interface
   public :: gpu_enabled, gpu_init, gpu_end
   public :: gpu_wfn_handle, gpu_promol_handle, gpu_set_core, gpu_destroy
   public :: gpu_cube, gpu_nciplot, gpu_nci_cutoffs, gpu_promolecular_grid, gpu_fillmesh, gpu_fillmesh_mo
+  public :: gpu_fragment_handle, gpu_nci_fragments, gpu_nci_cutoffs_frag
+  public :: gpu_write_cube_body, gpu_write_dat
 
   logical, save :: gpu_enabled = .false. !< set by the GPU keyword (global@proc.f90, critic_setvariables)
 
@@ -135,6 +137,11 @@ module gpu_interface
        character(kind=c_char) :: text(*)
        integer(c_int) :: ierr
      end function c2gpu_cube_text
+     function c2gpu_dat_text_size(npairs) bind(c,name="c2gpu_dat_text_size") result(nbytes)
+       import :: c_long
+       integer(c_long), value :: npairs
+       integer(c_long) :: nbytes
+     end function c2gpu_dat_text_size
      function c2gpu_dat_text(npairs,dat,text) bind(c,name="c2gpu_dat_text") result(ierr)
        import :: c_int, c_long, c_double, c_char
        integer(c_long), value :: npairs
@@ -547,6 +554,35 @@ contains
     close(lu)
     ok = .true.
   end subroutine gpu_write_cube_body
+
+  !> The (rho,s) lines of the NCIPLOT .dat file, '(1p,E15.7,E15.7)' (nci@proc.f90:593-595), appended to `file` through a
+  !> stream-access unit like gpu_write_cube_body: dat(2,ndat) are the pairs gpu_nci_cutoffs / gpu_nci_cutoffs_frag return.
+  subroutine gpu_write_dat(file,dat,ndat,ok)
+    character*(*), intent(in) :: file
+    real(c_double), intent(in) :: dat(2,*)
+    integer, intent(in) :: ndat
+    logical, intent(out) :: ok
+    character(kind=c_char), allocatable :: text(:)
+    integer(c_int) :: ierr
+    integer(c_long) :: nbytes
+    integer :: lu
+    ok = .false.
+    if (.not.gpu_enabled) return
+    if (ndat <= 0) then
+       ok = .true.
+       return
+    end if
+    nbytes = c2gpu_dat_text_size(int(ndat,c_long))
+    if (nbytes <= 0) return
+    allocate(text(nbytes))
+    ierr = c2gpu_dat_text(int(ndat,c_long),dat,text)
+    call gpu_check("write_dat",ierr)
+    if (ierr /= 0) return
+    open(newunit=lu,file=file,access='stream',form='unformatted',position='append',status='old')
+    write(lu) text
+    close(lu)
+    ok = .true.
+  end subroutine gpu_write_dat
 
   !> Replacement of the promolecular_grid loop (crystalmod@proc.f90:5143-5158): f(n1,n2,n3), nder = 0.
   subroutine gpu_promolecular_grid(h,n,f,ok)

@@ -109,6 +109,15 @@ int c2gpu_eval_grid_dev_part_rows(void *h, const double x0[3], const double xd[9
                                   int periodic, unsigned outmask, double *const *out_dev, int part, int nparts,
                                   void *stream);
 int c2gpu_layer_height(void *h);
+/* Gather leg of that model ("each GPU D2H-copies straight into its slice of the pinned host array"): the
+   blocks part `part` owns (rows = 0: layers, the decomposition of c2gpu_eval_grid_dev_part / c2gpu_nci_grid_dev_part;
+   rows = 1: rows of super-tiles, c2gpu_eval_grid_dev_part_rows) go from the part's full-size device arrays into the same
+   places of full-size host arrays; nci_order = 1 for crho/cgrad/rhoat (z fastest, x-layers).  With one shared page-locked
+   host buffer all ranks copy at once over their own PCIe links; pageable destinations are staged through the handle's
+   pinned bounce buffers.  Ordered after the work queued on `stream`; synchronous on return.  Replaces the writer-rank
+   gather the reference does not need (its arrays are already in the one process: rhoplot@proc.f90:582, nci@proc.f90:458). */
+int c2gpu_gather_part_host(void *h, const int nn[3], int nci_order, int narr, double *const *dev_arr,
+                           double *const *host_arr, int part, int nparts, int rows, void *stream);
 
 /* ---- NCIPLOT: evaluation loop src/nci@proc.f90:499-561, cutoff pass :569-604 ---------------------------------- */
 /* crho/cgrad/rhoat are (0:n3-1,0:n2-1,0:n1-1): z fastest, x slowest (:458-469).  hpromol/rhoat may be NULL. */
@@ -197,6 +206,10 @@ int c2gpu_wfn_count_active(void *h, const double x0[3], const double xd[9], cons
 /* Sum over the grid of the number of atoms inside the promolecular cutoffs (src/environmod@proc.f90:1284-1300). */
 int c2gpu_promol_count_active(void *h, const double x0[3], const double xd[9], const int nn[3], int periodic,
                               double *sum_nat);
+/* FP64 peaks of the first device, measured now (~0.1 s): chains of independent mma.sync m8n8k4 f64 (DMMA, the tensor
+   roofline of the wavefunction kernels) and of independent DFMAs (the roofline of the primitive / promolecular kernels).
+   bench.py prints them beside the recorded figures it normalises with. */
+int c2gpu_fp64_peak(double *dmma_tflops, double *dfma_tflops);
 /* Kernel configuration chosen for a wavefunction handle: points per tile, MO columns per block, blocks, threads. */
 int c2gpu_wfn_config(void *h, int cfg[8]);
 /* The configuration id wfn_create picks for an occupied-MO count (no device needed): 0 S1, 7 S3w, 8 M2, 4 L1, 6 WS. */

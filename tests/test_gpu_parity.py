@@ -843,3 +843,40 @@ def test_libxc_reference_energies_through_the_point_list_path(G, O):
     check_rho(res[:, 0], ref[:, 0])
     check_vec(res[:, 13:14], ref[:, 13:14], "gmod", rho=ref[:, 0])
     print(got)
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_gather_part_host_reassembles_the_grid(G, pinned):
+    """c2gpu_gather_part_host: each part copies the units it evaluated (layers / rows of super-tiles, CUBE and NCIPLOT
+    orders) from its own full-size device arrays into ONE host buffer; together they reproduce the one-launch result bit for
+    bit, through the pinned bounce buffers (pageable destination) and by direct DMA (page-locked destination)."""
+    import torch
+    from critic2_b200 import drivers, synth
+    f = synth.small_synthetic()
+    st = cases.mol_structure(f)
+    fld = G.WfnField(f, st)
+    x0, xd, nn = cases.bbox_grid(st, (21, 19, 26), margin=3.0)
+    npt = int(np.prod(nn))
+    props = ("f", "gy", "hxz")
+    full = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in props]
+    fld.cube_dev(x0, xd, nn, full, props)
+    mk_host = (lambda n: torch.full((n,), -7.0, dtype=torch.float64).pin_memory()) if pinned else \
+              (lambda n: torch.from_numpy(np.full(n, -7.0)))
+    for rows in (False, True):
+        host = [mk_host(npt) for _ in props]
+        for part in range(3):
+            outs = [torch.full((npt,), float("nan"), dtype=torch.float64, device="cuda") for _ in props]
+            fld.cube_dev_part(x0, xd, nn, outs, props, part, 3, rows=rows)
+            fld.gather_part_host(nn, outs, [t.data_ptr() for t in host], part, 3, rows=rows)
+        for h_, f_ in zip(host, full):
+            assert torch.equal(h_, f_.cpu())
+    xn, xm, ns = drivers.nci_grid(st, nstep=(27, 13, 11))
+    nptn = int(np.prod(ns))
+    frho, fgrad = (torch.zeros(nptn, dtype=torch.float64, device="cuda") for _ in range(2))
+    fld.nci_dev(xn, xm, ns, frho, fgrad)
+    host = [mk_host(nptn) for _ in range(2)]
+    for part in range(2):
+        outs = [torch.full((nptn,), float("nan"), dtype=torch.float64, device="cuda") for _ in range(2)]
+        fld.nci_dev_part(xn, xm, ns, outs[0], outs[1], part, 2)
+        fld.gather_part_host(ns, outs, [t.data_ptr() for t in host], part, 2, nci_order=True)
+    assert torch.equal(host[0], frho.cpu()) and torch.equal(host[1], fgrad.cpu())

@@ -112,18 +112,25 @@ def _gloo_worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     from critic2_b200 import sharding
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
-    nz, lh, plane = 21, 4, 6
-    truth = torch.arange(nz * plane, dtype=torch.float64).reshape(nz, plane) * 0.5 + 1.0
-    full = torch.full((nz, plane), 7.0, dtype=torch.float64)     # garbage outside the rank's layers
-    for c0, c1 in sharding.rank_layers(nz, lh, rank, world):
-        full[c0:c1] = truth[c0:c1]                                # "evaluate" own layers
-    sharding.zero_foreign_layers(full, nz, lh, rank, world)
-    sharding.gather_layers(full, nz, lh, rank, world, dist, dst=0)
+    # the gather of the one-process-per-GPU model: every rank copies the blocks it owns into ONE shared host buffer
+    # (SharedPinned; here without cudaHostRegister) -- layers and rows of super-tiles
+    nz, ny, nx, lh = 21, 13, 6, 4
+    truth = np.arange(nz * ny * nx, dtype=np.float64) * 0.5 + 1.0
+    sp = sharding.SharedPinned(rank, world, dist, register=False)
+    gathered = []
+    for k, rows in enumerate((False, True)):
+        shared = sp.get(truth.nbytes, f"t{k}")
+        mine = np.full(truth.shape, 7.0)                              # garbage outside the rank's blocks
+        sharding.copy_owned_blocks(mine, truth, nz, ny, lh, rank, world, rows=rows)   # "evaluate" the own blocks
+        sharding.copy_owned_blocks(shared, mine, nz, ny, lh, rank, world, rows=rows)  # the gather
+        dist.barrier()
+        gathered.append(bool(np.array_equal(shared, truth)))
     sums = torch.tensor([1.0 + rank, 2.0, 3.0], dtype=torch.float64)
     sharding.reduce_void_sums(sums, dist)
     ok = bool(torch.equal(sums, torch.tensor([3.0, 4.0, 6.0], dtype=torch.float64)))
-    if rank == 0:
-        ok = ok and bool(torch.equal(full, truth))
+    ok = ok and all(gathered)
+    dist.barrier()
+    sp.close()
     q.put((rank, ok))
     dist.destroy_process_group()
 
@@ -146,6 +153,7 @@ def test_rank_rows_tile_the_grid():
 
 
 def test_two_rank_gather_and_reduction_over_gloo():
+    """world_size-2 gloo run of the N > 1 host logic: shared-buffer gather (layers and rows) + void-sum reduction"""
     import torch.multiprocessing as mp
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -264,3 +272,27 @@ def test_fortran_shim_matches_the_c_header():
             # type(c_ptr), value carries a C pointer by value: allowed for pointer parameters (handles, nullable arrays)
             if not is_ptr:
                 assert n in byval, f"{cname}: {n} must be passed by value"
+
+
+def test_fortran_shim_exports_every_name_the_integration_notes_use():
+    """Every gpu_* entity INTEGRATION.md's call-site patches use must be PUBLIC in the (private-by-default) module
+    gpu_interface, every public name must be defined there, and every c2gpu_* the wrappers call must have a bind(c)
+    interface -- the checks a Fortran compiler would make at `use gpu_interface`."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "fortran", "gpu_interface.f90")).read()
+    src_nc = "\n".join(line.split("!")[0] for line in src.split("\n"))           # comments stripped
+    src_j = re.sub(r"&\s*\n\s*&?", "", src_nc)
+    public = set()
+    for m in re.finditer(r"^\s*public\s*::\s*(.*)$", src_j, flags=re.M):
+        public.update(n.strip() for n in m.group(1).split(","))
+    defined = set(re.findall(r"^\s*(?:subroutine|function)\s+(gpu_\w+)", src_j, flags=re.M))
+    defined |= set(re.findall(r"::\s*(gpu_\w+)\s*=", src_j))                      # module variables (gpu_enabled)
+    assert public <= defined, public - defined
+    notes = open(os.path.join(root, "INTEGRATION.md")).read()
+    used = set(re.findall(r"\bgpu_[a-z_0-9]+", notes)) - {"gpu_interface"}
+    used = {u for u in used if not u.endswith(".f90")}
+    assert used <= public, f"used in INTEGRATION.md but not public: {sorted(used - public)}"
+    bound = set(re.findall(r"bind\(c,name=\"(c2gpu_\w+)\"\)", src_j))
+    called = set(re.findall(r"\b(c2gpu_\w+)\s*\(", src_j))
+    assert called <= bound, called - bound
