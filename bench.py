@@ -331,9 +331,13 @@ def run_ours(a):
         raise SystemExit("bench.py: no CUDA device -- the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     shared = None
+    # stdout carries exactly one JSON line: everything native libraries print there (NCCL writes its version banner to
+    # stdout whatever NCCL_DEBUG_FILE says) is sent to stderr; the line itself goes to the saved descriptor
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if world > 1:
-        # rank 0 prints exactly one JSON line on stdout; NCCL's log (whatever level the caller asked for) goes to stderr
-        os.environ.setdefault("NCCL_DEBUG", "WARN")
+        os.environ.setdefault("NCCL_DEBUG", "WARN")      # the caller's level (e.g. INFO for a rank check) is kept
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         shared = sharding.SharedPinned(rank, world, dist)
@@ -535,7 +539,7 @@ def run_ours(a):
             line["e2e_single_process"] = e2e_sp
         if aux:
             line["aux"] = aux
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=json_out, flush=True)
         bad = [("headline", parity)] + [(f"cfg{d.get('cfg')}", d.get("parity")) for d in aux]
         for name, p in bad:
             if p is not None and not p.get("ok", True):

@@ -235,6 +235,10 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
   h->cfg = wfn_choose_config(nmoocc, g_force_cfg);
   // the split-producer kernel keeps every chi tile of a sub-tile in its cache: 80 KB per 32 primitives and CTA
   if (h->cfg == 6 && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 3;
+  if (h->cfg >= 9 && h->cfg <= 11 && nmoocc > wfn_cfg_info(h->cfg).NB) {   // the warp kernel holds ONE block of MO columns
+    delete h;
+    return fail(1, "c2gpu_wfn_create: the forced warp-kernel configuration holds fewer MO columns than nmoocc");
+  }
   const WfnCfgInfo &ci = wfn_cfg_info(h->cfg);
   h->nblk = (nmoocc + ci.NB - 1) / ci.NB;
   const int ldc = h->nblk * ci.NB;
@@ -254,6 +258,8 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     if (!newshell) {
       int j = ord[p - 1];
       newshell = icenter[i] != icenter[j] || expo[i] != expo[j] || dran[i] != dran[j];
+      // at most 21 primitives (a full Cartesian h shell) per device shell: the warp kernel's list holds 32 shells per step
+      newshell = newshell || p - shell_pbeg.back() >= 21;
     }
     if (newshell) {
       const double *c = xyz + 3 * (size_t)(icenter[i] - 1);

@@ -1,6 +1,7 @@
 // wfn_launch.cu -- instantiations and launch dispatch of the wavefunction grid kernel (sm_100a).
 #include "c2gpu_internal.h"
 #include "wfn_ws_kernel.cuh"
+#include "wfn_warp_kernel.cuh"
 
 namespace c2 {
 
@@ -25,6 +26,12 @@ long g_launches = 0;
 #define C2_WFN_CONFIGS2(X) \
   X(7, "S3w", 4, 3, 3, 12, 2) \
   X(8, "M2", 2, 4, 8, 16, 2)
+
+// warp-autonomous kernel (ids 9, 10, 11): NF fragments of 8 MO columns, CTAs per SM (register budget: 65536 / (128 x CTAS))
+#define C2_WARP_CONFIGS(X) \
+  X(1, 4)                  \
+  X(2, 3)                  \
+  X(3, 2)
 
 static void tile_shape(int P, int &ta, int &tb, int &tc) {
   switch (P) {
@@ -71,6 +78,18 @@ static std::vector<WfnCfgInfo> build_infos() {
   }
   C2_WFN_CONFIGS2(X)
 #undef X
+  // ids 9, 10, 11: warp-autonomous kernel (wfn_warp_kernel.cuh) with 1, 2, 3 fragments of 8 MO columns
+#define W(NF, CT)                                                                                   \
+  {                                                                                                 \
+    WfnCfgInfo i;                                                                                   \
+    i.name = "W" #NF; i.wm = 1; i.wn = 4; i.ni = NF; i.kc = 4; i.ctas = CT;                        \
+    i.P = 8; i.NB = 8 * NF; i.NT = WarpCfg<10, NF, CT>::NT;                                         \
+    tile_shape(i.P, i.ta, i.tb, i.tc);                                                              \
+    i.smem[0] = i.smem[1] = i.smem[2] = 0;                                                          \
+    v.push_back(i);                                                                                 \
+  }
+  C2_WARP_CONFIGS(W)
+#undef W
   return v;
 }
 
@@ -84,8 +103,9 @@ const WfnCfgInfo &wfn_cfg_info(int cfg) { return infos()[cfg]; }
 int wfn_choose_config(int nmo, int force) {
   if (force >= 0 && force < wfn_num_configs()) return force;
   int nfrag = (nmo + 7) / 8;
-  if (nfrag <= 1) return 0;
-  if (nfrag <= 3) return 7;
+  // up to 24 MOs: the warp-autonomous kernel (wfn_warp_kernel.cuh).  Measured on BASELINE config 1 (h2o-aqz 128^3, 5 MOs):
+  // 1.17 ms against 1.46 ms for S1; config 2 (benzene-adz NCIPLOT 200^3, 21 MOs): 13.4 ms against 17.3 ms for S3w
+  if (nfrag <= 3) return 8 + nfrag;
   // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms): M2 54 per 64-column block, L 97 per 112-column
   // block, the warp-specialised kernel 96 + 52 per 112-column block (its generators run ahead and the chi tiles are
   // re-used from the L2 cache, which only pays from three blocks up).  tools/probe_mid.py reproduces the table:
@@ -130,7 +150,22 @@ static cudaError_t launch_ws(const WfnParams &p, int grid, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+template <class C>
+static cudaError_t launch_warp(const WfnParams &p, int grid, cudaStream_t st) {
+  wfn_warp_kernel<C><<<grid, C::NT, 0, st>>>(p);
+  g_launches++;
+  return cudaGetLastError();
+}
+
 cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream_t st) {
+#define W(NF, CT)                                                        \
+  if (cfg == 8 + NF) {                                                   \
+    if (nd == 1) return launch_warp<WarpCfg<1, NF, CT>>(p, grid, st);    \
+    if (nd == 4) return launch_warp<WarpCfg<4, NF, CT>>(p, grid, st);    \
+    return launch_warp<WarpCfg<10, NF, CT>>(p, grid, st);                \
+  }
+  C2_WARP_CONFIGS(W)
+#undef W
   if (cfg == 6) {
     if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);
     if (nd == 4) return launch_ws<WsCfg<4>>(p, grid, st);

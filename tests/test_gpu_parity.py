@@ -72,10 +72,11 @@ def test_cube_cell_grid_ragged(G, O):
     assert (ref["f"] == 0).any()
 
 
-@pytest.mark.parametrize("cfg", [1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_all_configs(G, O, cfg, variant):
-    """24-atom def2-TZVP-shaped synthetic molecule through the M / L / L1 tensor-core tile configurations."""
+    """24-atom def2-TZVP-shaped synthetic molecule through every block-synchronous and warp-specialised configuration
+    (several MO blocks for the small ones: 42 / 85 MOs in blocks of 8, 24, 64, 112)."""
     from critic2_b200 import synth
     f = synth.small_synthetic(uhf=(variant != "rhf"), with_edf=(variant != "rhf"))
     st = cases.mol_structure(f)
@@ -619,7 +620,11 @@ def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
     from critic2_b200 import drivers
     f = cases.golden_wfn("benzene-adz")
     st = cases.mol_structure(f)
-    fld = G.WfnField(f, st)
+    G.set_option("wfn_cfg", 7)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
     assert fld.config()["cfg"] == 7
     x0, xmat, ns = drivers.nci_grid(st, nstep=(27, 19, 22))
     npt = int(np.prod(ns))
@@ -880,3 +885,104 @@ def test_gather_part_host_reassembles_the_grid(G, pinned):
         fld.nci_dev_part(xn, xm, ns, outs[0], outs[1], part, 2)
         fld.gather_part_host(ns, outs, [t.data_ptr() for t in host], part, 2, nci_order=True)
     assert torch.equal(host[0], frho.cpu()) and torch.equal(host[1], fgrad.cpu())
+
+
+# ---- round 2: the warp-autonomous kernel for small MO counts (csrc/wfn_warp_kernel.cuh; configurations 9, 10, 11) ----------
+@pytest.mark.parametrize("name,cfg", [("h2o-aqz", 9), ("h2o-aqz", 11), ("h2o-wfx", 9), ("hooh-atz", 10), ("benzene-adz", 11),
+                                      ("synth7", 9), ("synth16u", 10), ("synth24u", 11)])
+def test_warp_kernel_cube(G, O, name, cfg):
+    """CUBE through the warp kernel with 1, 2 and 3 fragments of 8 MO columns: s...g shells (h2o-aqz), Cartesian d/f
+    (hooh-atz), full and partly filled column blocks, UHF + EDF, ragged lattices (bricks cut by the grid edge)."""
+    from critic2_b200 import synth
+    if name.startswith("synth"):
+        u = name.endswith("u")
+        f = synth.small_synthetic(uhf=u, with_edf=u, nmo=int(name[5:].rstrip("u")))
+    else:
+        f = cases.golden_wfn(name)
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, (19, 15, 13), margin=3.0)
+    ref = _ofield(O, f, st).cube(x0, xd, nn)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    c = fld.config()
+    assert c["cfg"] == cfg and c["nblk"] == 1 and c["points_per_tile"] == 8
+    print(name, cfg, _compare_cube(fld.cube(x0, xd, nn), ref))
+
+
+@pytest.mark.parametrize("cfg", [9, 11])
+def test_warp_kernel_points_nder_nci_core_gkin_mo(G, O, cfg):
+    """Every driver through the warp kernel: ragged point list with nuclei, nder 0 / 1, NCIPLOT (two-pass and one-pass) with
+    its cutoff pass, core augmentation, gkin and MO values (value-only chi modes), interleaved parts."""
+    import torch
+    from critic2_b200 import drivers
+    f = cases.golden_wfn("benzene-adz" if cfg == 11 else "h2o-aqz")
+    st = cases.mol_structure(f)
+    of = _ofield(O, f, st)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+        assert fld.config()["cfg"] == cfg
+        rng = np.random.default_rng(17)
+        pts = np.concatenate([st.r[:3], st.r[0] + np.array([[3e-6, 0, 0]]),
+                              rng.uniform(st.r.min(0) - 3.0, st.r.max(0) + 3.0, (733, 3))])
+        ref = of.grd_points(pts, nder=2, periodic=True)
+        got = fld.points(pts, nder=2, periodic=True)
+        check_rho(got[:, 0], ref[:, 0])
+        check_vec(got[:, 1:4], ref[:, 1:4], "grad", rho=ref[:, 0])
+        check_vec(got[:, 4:13], ref[:, 4:13], "hess", rho=ref[:, 0])
+        assert np.array_equal(got[:, 15], ref[:, 15]) and ref[:4, 15].all() and not got[:4, 1:4].any()
+        x0, xd, nn = cases.bbox_grid(st, (13, 11, 9), margin=2.5)
+        grid_pts = np.array([x0 + xd @ np.array([i, j, k], float) for k in range(nn[2]) for j in range(nn[1]) for i in range(nn[0])])
+        for nder in (0, 1):
+            r = of.grd_points(grid_pts, nder=nder, periodic=False)
+            g = fld.cube(x0, xd, nn, nder=nder)
+            check_rho(g["f"].reshape(-1), r[:, 0])
+            if nder:
+                check_vec(np.stack([g[k].reshape(-1) for k in ("gx", "gy", "gz")], -1), r[:, 1:4], "grad", rho=r[:, 0])
+        xn, xm, ns = drivers.nci_grid(st, nstep=(17, 15, 14))
+        rrho, rgrad, _ = of.nci(xn, xm, ns)
+        crho, cgrad, _ = fld.nci(xn, xm, ns)
+        assert _nci_compare(crho, cgrad, rrho, rgrad) == 0
+        G.set_option("nci_two_pass", 0)
+        try:
+            c1, g1, _ = fld.nci(xn, xm, ns)
+        finally:
+            G.set_option("nci_two_pass", 1)
+        assert np.array_equal(c1, crho) and np.array_equal(g1, cgrad)
+        rg, cg = rgrad.copy(), cgrad.reshape(-1).copy()
+        _, rdat = O.nci_cutoffs(rrho.copy(), rg)
+        _, dat, ndat = G.nci_cutoffs(crho.reshape(-1), cg)
+        assert ndat == len(rdat) and np.array_equal(cg.reshape(rg.shape) == 100.0, rg == 100.0)
+        # kinetic energy density and MO values
+        rres = of.grd_points(pts, 1, True)
+        gk = fld.gkin_points(pts)
+        assert np.array_equal(gk == 0.0, rres[:, 17] == 0.0)
+        assert (np.abs(gk - rres[:, 17]) / np.maximum(rres[:, 17], 1e-30)).max() <= cases.TOL_DER
+        for imo in (1, f.nmoocc):
+            refm = of.mo_points(pts, imo, True)
+            gotm = fld.mo_points(pts, imo)
+            assert not gotm[refm == 0.0].any() and np.max(np.abs(gotm - refm)) <= cases.TOL_RHO * np.abs(refm).max()
+        # interleaved parts tile the grid bit for bit
+        npt = int(np.prod(nn))
+        full = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in range(2)]
+        fld.cube_dev(x0, xd, nn, full, ("f", "lap"))
+        for rows in (False, True):
+            acc = [torch.zeros(npt, dtype=torch.float64, device="cuda") for _ in range(2)]
+            for part in range(3):
+                outs = [torch.full((npt,), float("nan"), dtype=torch.float64, device="cuda") for _ in range(2)]
+                fld.cube_dev_part(x0, xd, nn, outs, ("f", "lap"), part, 3, rows=rows)
+                torch.cuda.synchronize()
+                for a_, o_ in zip(acc, outs):
+                    a_ += torch.nan_to_num(o_, nan=0.0)
+            assert all(torch.equal(a_, f_) for a_, f_ in zip(acc, full))
+        if cfg == 11:   # core augmentation (C zpsp 4)
+            ct = cases.core_tables()
+            fld.set_core(G.core_field(st, ct, {6: 4, 1: 0}))
+            ofc = O.Field(O.Environ(st), wfn=O.Wfn(f), core=O.Grid1Set({6: ct[(6, 4)]}))
+            _compare_cube(fld.cube(x0, xd, nn), ofc.cube(x0, xd, nn))
+            fld.set_core(None)
+    finally:
+        G.set_option("wfn_cfg", -1)

@@ -201,14 +201,14 @@ def test_chk_nci_checkpoint_round_trip(tmp_path, monkeypatch):
 
 
 def test_kernel_configuration_choice_follows_the_measured_cost_model():
-    """wfn_choose_config (no device needed): S1 up to 8 MOs, S3w up to 24, then the cheapest of M2 (64-column blocks, two CTAs
+    """wfn_choose_config (no device needed): the warp kernel with 1 / 2 / 3 column fragments up to 24 MOs, then the cheapest of M2 (64-column blocks, two CTAs
     per SM), L1 (112-column blocks, two CTAs per SM) and the warp-specialised kernel by the measured per-block costs (csrc/wfn_launch.cu)."""
     import ctypes as C
     from critic2_b200 import gpu
     L = C.CDLL(gpu.LIB_PATH)
     pick = lambda n: L.c2gpu_wfn_choose_config(n)
-    assert [pick(n) for n in (1, 5, 8)] == [0, 0, 0]
-    assert [pick(n) for n in (9, 21, 24)] == [7, 7, 7]
+    assert [pick(n) for n in (1, 5, 8)] == [9, 9, 9]
+    assert [pick(n) for n in (9, 16, 17, 21, 24)] == [10, 10, 11, 11, 11]
     assert [pick(n) for n in (25, 48, 64)] == [8, 8, 8]
     assert [pick(n) for n in (65, 100, 112)] == [4, 4, 4]
     assert [pick(n) for n in (113, 150, 192)] == [8, 8, 8]

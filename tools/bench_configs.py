@@ -33,6 +33,7 @@ def main(argv=None, cpu=None):
     ap.add_argument("--cfgs", default="1,2,3,5")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--force", default="", help="kernel configuration per BASELINE config, e.g. 1:0,2:7 (development A/B)")
     ap.add_argument("--cfg5-parts", type=int, default=8, help="time part 0 of this many interleaved parts of config 5")
     a = ap.parse_args(argv)
 
@@ -68,11 +69,19 @@ def main(argv=None, cpu=None):
 
 
     cfgs = [int(c) for c in a.cfgs.split(",")]
+    force = {int(k): int(v) for k, v in (kv.split(":") for kv in a.force.split(",") if kv)}
+
+    def wfn_field(which, f, st):
+        gpu.set_option("wfn_cfg", force.get(which, -1))
+        try:
+            return gpu.WfnField(f, st)
+        finally:
+            gpu.set_option("wfn_cfg", -1)
 
     if 1 in cfgs:   # h2o-aqz, CUBE CELL 128^3, f + gradient + Laplacian (one nder=2 evaluation)
         f = cases.golden_wfn("h2o-aqz")
         st = structure.molecular_cell(f.xyz, f.z)
-        fld = gpu.WfnField(f, st)
+        fld = wfn_field(1, f, st)
         x0, xd, nn = drivers.cube_grid(st, [128] * 3)
         props = ["f", "gx", "gy", "gz", "lap"]
         npts = int(np.prod(nn))
@@ -94,7 +103,7 @@ def main(argv=None, cpu=None):
     if 2 in cfgs:   # benzene-adz NCIPLOT 200^3 + cutoff pass
         f = cases.golden_wfn("benzene-adz")
         st = structure.molecular_cell(f.xyz, f.z)
-        fld = gpu.WfnField(f, st)
+        fld = wfn_field(2, f, st)
         x0, xmat, ns = drivers.nci_grid(st, nstep=[200] * 3)
         npts = int(np.prod(ns))
         crho, cgrad = zeros(npts, 2)
