@@ -127,6 +127,10 @@ double nci_const() {   // src/nci@proc.f90:86-87, evaluated at run time like the
 
 }  // namespace
 
+namespace c2 {
+int c2_fail(int code, const std::string &msg) { return fail(code, msg); }
+}  // namespace c2
+
 extern "C" {
 
 int c2gpu_init(int ndev_req, int *ndev) {

@@ -41,4 +41,7 @@ cudaError_t format_records_launch(const double *g_dev, char *text_dev, long nrec
 
 extern long g_launches;       // kernels launched by the library
 
+// sets the message c2gpu_last_error returns and hands `code` back (for entry points defined outside c2gpu.cu)
+int c2_fail(int code, const std::string &msg);
+
 }  // namespace c2

@@ -209,4 +209,75 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
   return cudaGetLastError();
 }
 
+// ---- allocation-free variant of the cutoff pass (c2gpu_nci_cutoffs_dev_noalloc, include/c2gpu.h) ------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The scratch of the three kernels above -- totals, per-block partial sums, per-block offsets, per-block counts -- lives in
+// ONE file-scope device array sized for the largest grid the entry accepts; every GPU that loads the library holds these
+// 2.25 MiB until exit.  In HOST code the array's name is only a stand-in for the symbol: its device address is asked for
+// once per device (that device current) with cudaGetSymbolAddress and that pointer is what the kernels receive.
+// Every call shares the array and finds the previous call's contents in it.  Nothing in it has to start at zero: a call
+// with nblk blocks rewrites out[0..3] and entries [0, nblk) of the three per-block arrays before reading them, and reads
+// nothing beyond nblk.  Two calls that overlap on one GPU (different streams, threads or processes sharing the context)
+// race on it.
+constexpr long NOALLOC_MAX_POINTS = 1L << 27;                                   // 134 217 728 = 512^3 (BASELINE config 5)
+constexpr long NOALLOC_MAX_BLK = (NOALLOC_MAX_POINTS + CUT_BLK - 1) / CUT_BLK;   // 65 536 blocks of 2 048 points
+constexpr size_t NOALLOC_O_BSUM = 256;                                           // out[4] in the first 256 bytes
+constexpr size_t NOALLOC_O_BOFF = NOALLOC_O_BSUM + sizeof(double) * 3 * NOALLOC_MAX_BLK;
+constexpr size_t NOALLOC_O_BCOUNT = NOALLOC_O_BOFF + sizeof(unsigned long long) * NOALLOC_MAX_BLK;
+constexpr size_t NOALLOC_BYTES = NOALLOC_O_BCOUNT + sizeof(unsigned) * NOALLOC_MAX_BLK;   // 2 359 552 bytes
+static __device__ __align__(256) unsigned char g_cut_scratch[NOALLOC_BYTES];
+
+static cudaError_t noalloc_scratch_address(unsigned char **ptr) {
+  static unsigned char *s_addr[64] = {nullptr};     // per device: the symbol has one instance (and address) per GPU
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!s_addr[dev]) {
+    void *d = nullptr;
+    if ((e = cudaGetSymbolAddress(&d, g_cut_scratch)) != cudaSuccess) return e;
+    s_addr[dev] = static_cast<unsigned char *>(d);
+  }
+  *ptr = s_addr[dev];
+  return cudaSuccess;
+}
+
 }  // namespace c2
+
+extern "C" int c2gpu_nci_cutoffs_dev_noalloc(long npts, const double *crho_dev, double *cgrad_dev, const double *rhoat_dev,
+                                             double rhocut, double dimcut, double rhoplot, const double srhorange[2],
+                                             int onlyneg, double rho_void, double raw_sums[3], long *ndat, double *dat_dev,
+                                             long maxdat, void *stream) {
+  using namespace c2;
+  if (!raw_sums || !ndat || !srhorange) return c2_fail(1, "c2gpu_nci_cutoffs_dev_noalloc: null argument");
+  raw_sums[0] = raw_sums[1] = raw_sums[2] = 0.0;
+  *ndat = 0;
+  if (npts <= 0) return 0;
+  if (npts > NOALLOC_MAX_POINTS)
+    return c2_fail(1, "c2gpu_nci_cutoffs_dev_noalloc: " + std::to_string(npts) + " points exceed the static scratch limit of " +
+                          std::to_string(NOALLOC_MAX_POINTS) + " (512^3); use c2gpu_nci_cutoffs_dev");
+  if (!crho_dev || !cgrad_dev) return c2_fail(1, "c2gpu_nci_cutoffs_dev_noalloc: null device array");
+  if (rho_void > 0.0 && !rhoat_dev) return c2_fail(1, "c2gpu_nci_cutoffs_dev_noalloc: VOID needs rhoat");
+  unsigned char *scr = nullptr;
+  cudaError_t e = noalloc_scratch_address(&scr);
+  if (e != cudaSuccess) return c2_fail(2, std::string("cudaGetSymbolAddress(g_cut_scratch): ") + cudaGetErrorString(e));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CutArgs a{npts, crho_dev, cgrad_dev, rhoat_dev, rhocut * 100.0, dimcut, rhoplot * 100.0, srhorange[0] * 100.0,
+            srhorange[1] * 100.0, rho_void, onlyneg, 0, nullptr, 0.95, 0.75};
+  const int nblk = (int)((npts + CUT_BLK - 1) / CUT_BLK);
+  double *out = reinterpret_cast<double *>(scr), *bsum = reinterpret_cast<double *>(scr + NOALLOC_O_BSUM);
+  unsigned long long *boff = reinterpret_cast<unsigned long long *>(scr + NOALLOC_O_BOFF);
+  unsigned *bcount = reinterpret_cast<unsigned *>(scr + NOALLOC_O_BCOUNT);
+  cut_count_kernel<<<nblk, CUT_NT, 0, st>>>(a, bcount, bsum);
+  cut_scan_kernel<<<1, 1024, 0, st>>>(nblk, bcount, boff, bsum, out);
+  cut_emit_kernel<<<nblk, CUT_NT, 0, st>>>(a, boff, dat_dev, maxdat);
+  g_launches += 3;
+  double h[4];
+  e = cudaMemcpyAsync(h, out, sizeof(h), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) return c2_fail(2, std::string("c2gpu_nci_cutoffs_dev_noalloc: ") + cudaGetErrorString(e));
+  *ndat = (long)h[0];
+  raw_sums[0] = h[1]; raw_sums[1] = h[2]; raw_sums[2] = h[3];
+  return 0;
+}

@@ -69,6 +69,7 @@ def lib():
         L.c2gpu_nci_cutoffs_dev.argtypes = [C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                             C.c_double, dp, C.c_int, C.c_double, dp, C.POINTER(C.c_long), C.c_void_p,
                                             C.c_long, C.c_void_p]
+        L.c2gpu_nci_cutoffs_dev_noalloc.argtypes = L.c2gpu_nci_cutoffs_dev.argtypes
         L.c2gpu_nci_fragments.argtypes = [C.c_int, C.POINTER(C.c_void_p), dp, dp, ip, dp]
         L.c2gpu_nci_fragments_dev.argtypes = [C.c_int, C.POINTER(C.c_void_p), dp, dp, ip, C.c_void_p, C.c_int, C.c_int,
                                               C.c_void_p]

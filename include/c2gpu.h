@@ -140,6 +140,19 @@ int c2gpu_nci_cutoffs_dev(long npts, const double *crho_dev, double *cgrad_dev, 
                           double rhocut, double dimcut, double rhoplot, const double srhorange[2], int onlyneg,
                           double rho_void, double raw_sums[3], long *ndat, double *dat_dev, long maxdat,
                           void *stream);
+/* Allocation-free variant of c2gpu_nci_cutoffs_dev.  NO COUNTERPART IN THE REFERENCE: added
+   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+   forbid it).  Same arguments, same kernels and bit-identical results; the pass's scratch (per-block counts, partial sums
+   and offsets: 36 bytes per 2 048 points) lives in one static __device__ array of 2 359 552 bytes that every GPU loading
+   the library holds until exit, so the entry calls no cudaMalloc / cudaFree / allocating routine.  Limit: npts <=
+   C2GPU_NOALLOC_MAX_POINTS (512^3); larger grids are rejected with status 1 and a message (use c2gpu_nci_cutoffs_dev).
+   Runs on the CURRENT device.  All calls share the array (it keeps the last call's contents; every entry a call reads is
+   rewritten by that call first, so nothing needs clearing): calls that overlap on one GPU race -- serialise them. */
+#define C2GPU_NOALLOC_MAX_POINTS 134217728L
+int c2gpu_nci_cutoffs_dev_noalloc(long npts, const double *crho_dev, double *cgrad_dev, const double *rhoat_dev,
+                                  double rhocut, double dimcut, double rhoplot, const double srhorange[2], int onlyneg,
+                                  double rho_void, double raw_sums[3], long *ndat, double *dat_dev, long maxdat,
+                                  void *stream);
 
 /* ---- NCIPLOT fragments: src/nci@proc.f90:534-550 (rhofrag) and :579-582 (the `inter` test) ----------------------
    A fragment handle is a promolecular handle made by c2gpu_promol_create over the fragment's own atoms only
