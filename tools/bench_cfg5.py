@@ -129,11 +129,11 @@ def run(rank, world, dev, dist=None, grid=512, steps=2, warmup=1, small=False, c
                                              C.c_void_p(g[2].data_ptr()), 0.2, 2.0, 0.1, gpu._d(sr), 0, RHO_VOID,
                                              gpu._d(sums), C.byref(nd), C.c_void_p(dat.data_ptr()), nsub, C.c_void_p(stream)))
         torch.cuda.synchronize()
+        # the sampled (j, k) sub-lattice of the plane as a lattice of its own, (j, k) on the two SLOWEST axes: same flat order
+        # (k fastest), and the oracle's OpenMP loop over the slowest index gets len(jj) iterations to spread over the cores
         xs = x0 + i * xmat[:, 0] + (sub // 2) * xmat[:, 1] + (sub // 2) * xmat[:, 2]
-        xm = xmat.copy()
-        xm[:, 1] *= sub
-        xm[:, 2] *= sub
-        parity, cpu_base = cpu.nci_parity(f, st, xs, xm, np.array([1, len(jj), len(kk)], np.int32),
+        xm = np.stack([sub * xmat[:, 1], sub * xmat[:, 2], xmat[:, 0]], 1)
+        parity, cpu_base = cpu.nci_parity(f, st, xs, xm, np.array([len(jj), len(kk), 1], np.int32),
                                           [t_.cpu().numpy() for t_ in g], gm.cpu().numpy(), sums, int(nd.value), RHO_VOID,
                                           f"x-plane {i} of {n1}, every {sub}th (j,k): {nsub} points")
     out = None
