@@ -320,8 +320,8 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
     void *d = nullptr;
     if (!rc && cudaMalloc(&d, sizeof(int) * per_cta * r.grid) == cudaSuccess) { r.allocs.push_back(d); r.scratch = (int *)d; } else rc = 2;
     if (!rc && cudaMalloc(&d, 64) == cudaSuccess) { r.allocs.push_back(d); r.counter = (int *)d; } else rc = 2;
-    if (!rc && h->cfg == 6) {
-      r.acache_chunks = (npri + 31) / 32;   // worst case: every primitive active in a sub-tile
+    if (!rc && wfn_is_ws(h->cfg)) {
+      r.acache_chunks = (npri + 31) / 32 + 2;   // worst case: every primitive active in a sub-tile (+ rounding to stages of up to 64)
       size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
       if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
       if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;

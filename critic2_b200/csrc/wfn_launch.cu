@@ -90,6 +90,15 @@ static std::vector<WfnCfgInfo> build_infos() {
   }
   C2_WARP_CONFIGS(W)
 #undef W
+  // id 12: the warp-specialised kernel with 96-column MO blocks: 3 + 3 fragments per SM sub-partition instead of the 4 + 3
+  // of the 112-column blocks (a lone 4-fragment warp cannot keep the DMMA pipe full while its 3-fragment partner waits at
+  // the stage barrier: tools/dmma_issue.cu).  128-column blocks (4 + 4) do not fit the register file (2 x 232 + 88 > 512).
+  {
+    WfnCfgInfo i = v[6];
+    i.name = "WS96"; i.ni = 12; i.NB = 96;
+    i.smem[0] = WsCfg<1, 12>::SMEM; i.smem[1] = WsCfg<4, 12>::SMEM; i.smem[2] = WsCfg<10, 12>::SMEM;
+    v.push_back(i);
+  }
   return v;
 }
 
@@ -166,6 +175,11 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
   }
   C2_WARP_CONFIGS(W)
 #undef W
+  if (cfg == 12) {
+    if (nd == 1) return launch_ws<WsCfg<1, 12>>(p, grid, st);
+    if (nd == 4) return launch_ws<WsCfg<4, 12>>(p, grid, st);
+    return launch_ws<WsCfg<10, 12>>(p, grid, st);
+  }
   if (cfg == 6) {
     if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);
     if (nd == 4) return launch_ws<WsCfg<4>>(p, grid, st);

@@ -17,7 +17,7 @@ namespace c2 {
 
 // NFRAG_ = 8-column fragments per MO block: 14 (NB = 112, large MO counts) or 8 (NB = 64, a few dozen to ~200 MOs, where
 // 112-column blocks would pad too much).  Warp columns 0,1 (warpgroup 0) own NF0 fragments each, 2,3 (warpgroup 1) NF1.
-template <int ND_, int NFRAG_ = 14>
+template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3>
 struct WsCfg {
   static constexpr int ND = ND_;
   static constexpr int P = 16, WM = 2;          // points per sub-tile (two 8-point MMA row groups)
@@ -27,15 +27,21 @@ struct WsCfg {
   static constexpr int NCW = 8, NPW = 4;        // consumer / producer warps
   static constexpr int NT = 32 * (NCW + NPW);
   static constexpr int NCT = 32 * NCW, NPT = 32 * NPW;
-  static constexpr int KC = 32, NKQ = KC / 4;   // primitives per stage
-  static constexpr int NS = 3;                  // stages
+  static constexpr int KC = KC_, NKQ = KC / 4;  // primitives per stage (<= 64: the streamer issues two rows per lane)
+  static constexpr int NS = NS_;                // stages
+  static constexpr int ACHUNK = 32 * ND * P;    // chi-cache doubles per 32 primitives (the unit of WfnParams::acache_chunks)
+  static_assert(KC % 4 == 0 && KC <= 64 && NKQ <= 32, "stage size");
   static constexpr int NI = NF0;                // most fragments per consumer warp
   static constexpr int SB = NB + 4;             // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
   static constexpr int TSLOTS = 8;              // tile-info ring (>= NS + 3, see ws_generator)
   static constexpr int NPART = 2 * 4 * P * ND;  // s_part doubles: [2 sub-tile parities][4 warp columns][P][ND]
   static constexpr size_t SMEM = sizeof(double) * (NS * (A_STAGE + B_STAGE) + NPART + TSLOTS * 4 * P) + 256;
-  static constexpr int REG_CONS4 = 232, REG_CONS3 = 184, REG_PROD = 88;   // per warpgroup (setmaxnreg)
+  // registers per warpgroup (setmaxnreg): 232 for four fragments (160 accumulator registers), 184 for three or fewer; the
+  // three budgets add up to the 3 x 168 of the launch
+  static constexpr int REG_CONS4 = NF0 >= 4 ? 232 : 184, REG_CONS3 = NF1 >= 4 ? 232 : 184;
+  static constexpr int REG_PROD = 504 - REG_CONS4 - REG_CONS3;
+  static_assert(REG_PROD >= 88 && REG_PROD % 8 == 0, "register budget of the producer warpgroup");
 };
 
 // Per-stage header written by the producers, read by the consumers.
@@ -275,7 +281,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       const int nch = (kact + KC - 1) / KC;
       const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
       const bool pvalid = tp[3 * P + pt] != 0.0;
-      double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::A_STAGE;
+      double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::ACHUNK;
       int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * 8;
       // ---- chi tiles: k-quad q = (chunk, quad within the chunk) -> 16-lane group q % NGRP ------------------------------
       const int nquad = nch * (KC / 4);
@@ -285,7 +291,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       bool pass = false;
       for (int q = grp; q < nquad; q += NGRP) {
         const double2 mine = reinterpret_cast<const double2 *>(rec + (size_t)q * 32)[pt];
-        double *Aq = agbase + (size_t)(q >> 3) * C::A_STAGE + (size_t)((q & 7) * ND) * P * 4 + pt * 4;
+        double *Aq = agbase + (size_t)q * ND * P * 4 + pt * 4;   // quads are contiguous: chunk c starts at c * A_STAGE
         unsigned nzbits = 0;
 #pragma unroll
         for (int k4 = 0; k4 < 4; k4++) {
@@ -360,7 +366,7 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
     const WsTileDesc td = S.tdesc[buf];
     if (td.flags & 1) break;
     const int2 *pr_list = pr_list0 + (size_t)buf * p.prim_cap;
-    const double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::A_STAGE;
+    const double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::ACHUNK;
     const int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * 8;
     const unsigned it0 = it;
     if (td.kact == 0) {   // nothing active: a data-less stage tells the consumers to emit zeros (+ EDF) for this tile
@@ -379,7 +385,8 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
           const int c = (blk & 1) ? td.nch - 1 - cc : cc;
           const int nrow = min(KC, td.kact - c * KC);
           const int prim = lane < nrow ? pr_list[c * KC + lane].x : 0;         // loads issued before the wait
-          const int nz = lane < C::NKQ ? nzbase[c * 8 + lane] : 0;
+          const int prim2 = (KC > 32 && lane + 32 < nrow) ? pr_list[c * KC + lane + 32].x : 0;
+          const int nz = lane < C::NKQ ? nzbase[c * C::NKQ + lane] : 0;
           const unsigned m0 = __ballot_sync(~0u, (nz & 1) != 0), m1 = __ballot_sync(~0u, (nz & 2) != 0);
           const int stg = acquire();
           if (lane == 0) {
@@ -397,6 +404,9 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
           __syncwarp();
           if (lane < nrow)
             tma_bulk_g2s(S.Bs + stg * C::B_STAGE + lane * SB, w.cmoT + (size_t)prim * w.ldc + (size_t)blk * NB,
+                         (uint32_t)(NB * sizeof(double)), &S.full[stg]);
+          if (KC > 32 && lane + 32 < nrow)
+            tma_bulk_g2s(S.Bs + stg * C::B_STAGE + (lane + 32) * SB, w.cmoT + (size_t)prim2 * w.ldc + (size_t)blk * NB,
                          (uint32_t)(NB * sizeof(double)), &S.full[stg]);
           it++;
         }
@@ -651,7 +661,7 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   __syncthreads();
   // setmaxnreg works per warpgroup (4 warps): 128 x (232 + 184 + 88) = 64512 registers = 384 x 168, the launch figure
   if (tid >= C::NCT) {
-    reg_dec<C::REG_PROD>();
+    if (C::REG_PROD <= 168) reg_dec<C::REG_PROD>(); else reg_inc<C::REG_PROD>();
     if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
     else ws_generator<C>(p, S, tid - C::NCT - 32);
   } else if (tid < 128) {

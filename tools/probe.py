@@ -16,10 +16,11 @@ ap.add_argument("--z0", type=int, default=192)
 ap.add_argument("--z1", type=int, default=208)
 ap.add_argument("--cfgs", type=str, default="3,4")
 ap.add_argument("--small", action="store_true")
+ap.add_argument("--nmo", type=int, default=0, help="MO count of the config-4 molecule (default 780)")
 a = ap.parse_args()
 
 gpu.init_devices([0])
-f = synth.small_synthetic() if a.small else synth.config4()
+f = synth.small_synthetic() if a.small else (synth.synthetic_molecule(nmo=a.nmo) if a.nmo else synth.config4())
 st = structure.molecular_cell(f.xyz, f.z)
 lo, hi = st.r.min(0) - 6.0, st.r.max(0) + 6.0
 nn = np.array([a.n] * 3, np.int32)
@@ -41,7 +42,9 @@ for cfg in [int(c) for c in a.cfgs.split(",")]:
         e1.record()
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
-        print(f"cfg {cfg} {fld.config()} slab [{a.z0},{a.z1}) {npts} pts mean n_act {nact / npts:.1f} "
+        c_ = fld.config()
+        print(f"nmo {f.nmoocc} padded {c_['nblk'] * c_['mo_block']} ms/column {ms / (c_['nblk'] * c_['mo_block']):.4f} | "
+              f"cfg {cfg} {fld.config()} slab [{a.z0},{a.z1}) {npts} pts mean n_act {nact / npts:.1f} "
               f"{ms:.1f} ms -> {npts / ms * 1e3:.3e} pts/s, {flops / ms / 1e9:.2f} TFLOP/s algorithmic "
               f"({flops / ms / 1e9 / 37.1 * 100:.1f}% of 37.1)", flush=True)
     fld.close()
