@@ -425,11 +425,18 @@ def run_ours(a):
             hbuf = shared.get(len(PROPS10) * npts_total * 8, "cfg4")
             hptr = [hbuf.ctypes.data + k * npts_total * 8 for k in range(len(PROPS10))]
             d2h = len(PROPS10) * npts_total * 8
+            # two z-slabs when the per-rank copy is long enough (2-3 ranks: >= 70 ms) to pay for the tail of a second launch
+            # (super-tiles take ~14 ms each on this molecule); measured at N = 2: 6135 -> 6120 ms; one slab from 4 ranks up
+            nsl = 2 if world <= 3 else 1
+            zcut = [min(int(nn[2]), ((int(nn[2]) * k // nsl + lh - 1) // lh) * lh) for k in range(nsl + 1)]
+            slabs = [(zcut[k], zcut[k + 1]) for k in range(nsl) if zcut[k + 1] > zcut[k]]
             for it in range(1 + a.e2e_calls):
                 sync()
                 t0 = time.perf_counter()
-                fld.cube_dev_part(lo, xd, nn, outs, PROPS10, rank, world, stream=stream, rows=True)
-                fld.gather_part_host(nn, outs, hptr, rank, world, rows=True, stream=stream)
+                for z0, z1 in slabs:      # the copy of slab s runs behind the kernel of slab s + 1
+                    fld.cube_dev_part_range(lo, xd, nn, outs, PROPS10, rank, world, z0, z1, stream=stream, rows=True)
+                    fld.gather_part_host_range(nn, outs, hptr, rank, world, z0, z1, rows=True, async_=True, stream=stream)
+                fld.gather_wait()
                 dist.barrier()
                 if it > 0:
                     tes.append(time.perf_counter() - t0)
@@ -437,8 +444,9 @@ def run_ours(a):
             if rank == 0:
                 chk = float(hv[0].sum())
                 host_vals = np.stack([hv[k][flat_idx] for k in range(len(PROPS10))], 1)
-            note = (f"per-rank rows of super-tiles + c2gpu_gather_part_host into one shared page-locked host buffer ({world} "
-                    f"PCIe links in parallel, no inter-GPU traffic); mean of {a.e2e_calls} steps after one warm-up step")
+            note = (f"per-rank rows of super-tiles in {len(slabs)} z-slabs (c2gpu_eval_grid_dev_part_range), each followed by an "
+                    f"asynchronous c2gpu_gather_part_host_range into one shared page-locked host buffer ({world} PCIe links in "
+                    f"parallel, no inter-GPU traffic); mean of {a.e2e_calls} steps after one warm-up step")
         tt = torch.tensor([float(np.mean(tes)), float(np.min(tes)), float(np.max(tes))], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)

@@ -59,6 +59,12 @@ def lib():
         L.c2gpu_layer_height.argtypes = [C.c_void_p]
         L.c2gpu_gather_part_host.argtypes = [C.c_void_p, ip, C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                              C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.c2gpu_gather_part_host_range.argtypes = [C.c_void_p, ip, C.c_int, C.c_int, C.POINTER(C.c_void_p),
+                                                   C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                   C.c_void_p]
+        L.c2gpu_gather_wait.argtypes = [C.c_void_p]
+        L.c2gpu_eval_grid_dev_part_range.argtypes = [C.c_void_p, dp, dp, ip, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p),
+                                                     C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_nci_grid_dev_part.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, C.c_void_p, C.c_void_p, C.c_void_p,
                                               C.c_int, C.c_int, C.c_void_p]
         L.c2gpu_nci_grid.argtypes = [C.c_void_p, C.c_void_p, dp, dp, ip, dp, dp, dp]
@@ -220,6 +226,27 @@ class _Field:
         ptrs = (C.c_void_p * len(outs))(*[C.c_void_p(t.data_ptr()) for t in outs])
         fn = lib().c2gpu_eval_grid_dev_part_rows if rows else lib().c2gpu_eval_grid_dev_part
         _check(fn(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs, part, nparts, C.c_void_p(stream)))
+
+    def cube_dev_part_range(self, x0, xd, nn, outs, props, part: int, nparts: int, iz0: int, iz1: int, nder: int = 2,
+                            periodic: bool = False, stream: int = 0, rows: bool = True):
+        """cube_dev_part on the slab [iz0, iz1) of z planes (units counted from iz0)."""
+        x0a, xda, nna = _grid_args(x0, xd, nn)
+        names = [p for p in PROPS if p in props]
+        mask = sum(1 << PROPS.index(p) for p in names)
+        ptrs = (C.c_void_p * len(outs))(*[C.c_void_p(t.data_ptr()) for t in outs])
+        _check(lib().c2gpu_eval_grid_dev_part_range(self.handle, _d(x0a), _d(xda), _i(nna), nder, int(periodic), mask, ptrs,
+                                                    part, nparts, int(rows), iz0, iz1, C.c_void_p(stream)))
+
+    def gather_part_host_range(self, nn, dev_arrays, host_ptrs, part: int, nparts: int, c0: int, c1: int, rows: bool = True,
+                               nci_order: bool = False, async_: bool = True, stream: int = 0):
+        na = _i32(nn)
+        d = (C.c_void_p * len(dev_arrays))(*[C.c_void_p(t.data_ptr()) for t in dev_arrays])
+        hp = (C.c_void_p * len(host_ptrs))(*[C.c_void_p(int(p)) for p in host_ptrs])
+        _check(lib().c2gpu_gather_part_host_range(self.handle, _i(na), int(nci_order), len(dev_arrays), d, hp, part, nparts,
+                                                  int(rows), c0, c1, int(async_), C.c_void_p(stream)))
+
+    def gather_wait(self):
+        _check(lib().c2gpu_gather_wait(self.handle))
 
     def layer_height(self) -> int:
         return int(lib().c2gpu_layer_height(self.handle))

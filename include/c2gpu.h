@@ -118,6 +118,17 @@ int c2gpu_layer_height(void *h);
    gather the reference does not need (its arrays are already in the one process: rhoplot@proc.f90:582, nci@proc.f90:458). */
 int c2gpu_gather_part_host(void *h, const int nn[3], int nci_order, int narr, double *const *dev_arr,
                            double *const *host_arr, int part, int nparts, int rows, void *stream);
+/* The same two steps on a slab [iz0, iz1) of the slowest output axis (units counted from iz0; iz0 a multiple of the layer
+   height): a pass cut into 2-3 slabs lets the gather of slab s run behind the kernel of slab s + 1.  async_ = 1 queues the
+   copies behind the work already on `stream` and returns at once (page-locked host arrays only); c2gpu_gather_wait blocks
+   until every queued gather of the handle has landed. */
+int c2gpu_eval_grid_dev_part_range(void *h, const double x0[3], const double xd[9], const int nn[3], int nder,
+                                   int periodic, unsigned outmask, double *const *out_dev, int part, int nparts, int rows,
+                                   int iz0, int iz1, void *stream);
+int c2gpu_gather_part_host_range(void *h, const int nn[3], int nci_order, int narr, double *const *dev_arr,
+                                 double *const *host_arr, int part, int nparts, int rows, int c0, int c1, int async_,
+                                 void *stream);
+int c2gpu_gather_wait(void *h);
 
 /* ---- NCIPLOT: evaluation loop src/nci@proc.f90:499-561, cutoff pass :569-604 ---------------------------------- */
 /* crho/cgrad/rhoat are (0:n3-1,0:n2-1,0:n1-1): z fastest, x slowest (:458-469).  hpromol/rhoat may be NULL. */

@@ -875,6 +875,19 @@ def test_gather_part_host_reassembles_the_grid(G, pinned):
             fld.gather_part_host(nn, outs, [t.data_ptr() for t in host], part, 3, rows=rows)
         for h_, f_ in zip(host, full):
             assert torch.equal(h_, f_.cpu())
+        if pinned:   # the pass cut into z-slabs, every slab followed by an asynchronous ranged gather
+            host = [mk_host(npt) for _ in props]
+            for part in range(3):
+                outs = [torch.full((npt,), float("nan"), dtype=torch.float64, device="cuda") for _ in props]
+                for z0, z1 in ((0, 8), (8, 24), (24, 26)):
+                    fld.cube_dev_part_range(x0, xd, nn, outs, props, part, 3, z0, z1, rows=rows)
+                    fld.gather_part_host_range(nn, outs, [t.data_ptr() for t in host], part, 3, z0, z1, rows=rows, async_=True)
+                fld.gather_wait()
+            for h_, f_ in zip(host, full):
+                assert torch.equal(h_, f_.cpu())
+        else:
+            with pytest.raises(G.C2GpuError):   # an asynchronous gather into pageable memory is refused
+                fld.gather_part_host_range(nn, full, [t.data_ptr() for t in host], 0, 3, 0, 8, rows=rows, async_=True)
     xn, xm, ns = drivers.nci_grid(st, nstep=(27, 13, 11))
     nptn = int(np.prod(ns))
     frho, fgrad = (torch.zeros(nptn, dtype=torch.float64, device="cuda") for _ in range(2))
