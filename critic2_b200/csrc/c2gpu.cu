@@ -154,6 +154,7 @@ int c2gpu_init_devices(const int *devs, int n) {
 }
 
 int c2gpu_finalize(void) {
+  nci_cutoffs_release();
   g_devs.clear();
   return 0;
 }

@@ -35,6 +35,8 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
                                double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
                                double *raw_sums, long *ndat, double *dat_dev, long maxdat, cudaStream_t st);
 
+void nci_cutoffs_release();   // frees the per-device scratch of the cutoff pass
+
 // cube_format.cu: text records of cube / .dat files (fmt and order as in include/c2gpu.h)
 long format_record_bytes(int nval, int fmt);
 cudaError_t format_records_launch(const double *g_dev, char *text_dev, long nrec, int nval, int fmt, int order, int n1,

@@ -163,6 +163,23 @@ __global__ void __launch_bounds__(CUT_NT) cut_emit_kernel(CutArgs a, const unsig
   }
 }
 
+// per-device scratch of nci_cutoffs_launch, kept between calls (grow-only), released by c2gpu_finalize
+static unsigned char *s_scr[64] = {nullptr};
+static size_t s_cap[64] = {0};
+
+void nci_cutoffs_release() {
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (int d = 0; d < 64; d++)
+    if (s_scr[d]) {
+      cudaSetDevice(d);
+      cudaFree(s_scr[d]);
+      s_scr[d] = nullptr;
+      s_cap[d] = 0;
+    }
+  cudaSetDevice(prev);
+}
+
 cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, const double *rhoat, int nfrag,
                                const double *rhofrag, double rhoparam, double rhoparam2, double rhocut,
                                double dimcut, double rhoplot, double sr0, double sr1, int onlyneg, double rho_void,
@@ -175,8 +192,6 @@ cudaError_t nci_cutoffs_launch(long npts, const double *crho, double *cgrad, con
   int nblk = (int)((npts + CUT_BLK - 1) / CUT_BLK);
   // one scratch allocation: out[4] | bsum[3*nblk] | boff[nblk] (64-bit) | bcount[nblk]
   // kept per device between calls (grow-only): cudaMalloc + cudaFree cost more than the pass itself on a 200^3 grid
-  static unsigned char *s_scr[64] = {nullptr};
-  static size_t s_cap[64] = {0};
   const size_t o_bsum = 4 * sizeof(double), o_boff = o_bsum + sizeof(double) * 3 * (size_t)nblk;
   const size_t o_bcount = o_boff + sizeof(unsigned long long) * (size_t)nblk;
   const size_t need = o_bcount + sizeof(unsigned) * (size_t)nblk;

@@ -93,6 +93,8 @@ int c2gpu_field_set_core(void *handle, void *hcore);
 int c2gpu_eval_grid(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
                     unsigned outmask, double *const *out);
 /* slab [iz0,iz1) of the same loop into full-size DEVICE arrays */
+/* The *_dev entries run on the handle's first device and share that replica's work counter and scratch buffers: issue the
+   calls of ONE handle on ONE stream (or serialise them); different handles may run concurrently on different streams. */
 int c2gpu_eval_grid_dev(void *h, const double x0[3], const double xd[9], const int nn[3], int nder, int periodic,
                         unsigned outmask, double *const *out_dev, int iz0, int iz1, void *stream);
 
