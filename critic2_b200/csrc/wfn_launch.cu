@@ -99,6 +99,15 @@ static std::vector<WfnCfgInfo> build_infos() {
     i.smem[0] = WsCfg<1, 12>::SMEM; i.smem[1] = WsCfg<4, 12>::SMEM; i.smem[2] = WsCfg<10, 12>::SMEM;
     v.push_back(i);
   }
+  // id 13: the warp-specialised kernel for ONE TO FOUR MO blocks: 64-column blocks (two fragments per consumer warp), seven
+  // generator warps instead of three (512 threads, 128 registers each)
+  {
+    WfnCfgInfo i = v[6];
+    using W = WsCfg<10, 8, 32, 3, 8>;
+    i.name = "WS64g"; i.ni = 8; i.NB = 64; i.NT = W::NT;
+    i.smem[0] = WsCfg<1, 8, 32, 3, 8>::SMEM; i.smem[1] = WsCfg<4, 8, 32, 3, 8>::SMEM; i.smem[2] = W::SMEM;
+    v.push_back(i);
+  }
   return v;
 }
 
@@ -123,8 +132,13 @@ int wfn_choose_config(int nmo, int force) {
   //   L      103    103   197   197   197   197
   //   WS     148    148   200   200   200   200
   // L1 is L with 8-point sub-tiles and two CTAs per SM (224 threads each): 100.7 / 194.3 ms where L takes 103.2 / 197.9.
+  // WS64g (id 13: 64-column blocks, seven generator warps; same molecule, profiles/r2_probe_mid.log):
+  //   blocks   1     2     3     4     5      -> 92.6  119.5  157.4  198.2  239.7 ms: generator-bound up to two blocks, then
+  //   35 + 41 per block; it wins for 129-192, 225-320 and 337-384 MOs (256 MOs: 198 against 222 ms for M2, 67.9 % of the peak)
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
   const int tM = 54 * bM + 3, tL = 95 * bL + 6, tW = 96 + 52 * bL;
+  const int tG = bM <= 1 ? 93 : (bM == 2 ? 120 : 35 + 41 * bM);
+  if (tG < tM && tG < tL && tG < tW) return 13;
   if (tM <= tL && tM <= tW) return 8;
   return tL <= tW ? 4 : 6;
 }
@@ -179,6 +193,11 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
     if (nd == 1) return launch_ws<WsCfg<1, 12>>(p, grid, st);
     if (nd == 4) return launch_ws<WsCfg<4, 12>>(p, grid, st);
     return launch_ws<WsCfg<10, 12>>(p, grid, st);
+  }
+  if (cfg == 13) {
+    if (nd == 1) return launch_ws<WsCfg<1, 8, 32, 3, 8>>(p, grid, st);
+    if (nd == 4) return launch_ws<WsCfg<4, 8, 32, 3, 8>>(p, grid, st);
+    return launch_ws<WsCfg<10, 8, 32, 3, 8>>(p, grid, st);
   }
   if (cfg == 6) {
     if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);

@@ -17,14 +17,16 @@ namespace c2 {
 
 // NFRAG_ = 8-column fragments per MO block: 14 (NB = 112, large MO counts) or 8 (NB = 64, a few dozen to ~200 MOs, where
 // 112-column blocks would pad too much).  Warp columns 0,1 (warpgroup 0) own NF0 fragments each, 2,3 (warpgroup 1) NF1.
-template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3>
+// NPW_ = producer warps: 4 (one streamer + three generators; with 8 consumer warps 384 threads) or 8 (seven generators, 512
+// threads: for one to four MO blocks, where the generators -- not the tensor pipe -- set the pace).
+template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3, int NPW_ = 4>
 struct WsCfg {
   static constexpr int ND = ND_;
   static constexpr int P = 16, WM = 2;          // points per sub-tile (two 8-point MMA row groups)
   static constexpr int NFRAG = NFRAG_, NB = 8 * NFRAG_;    // MO columns per block
   static constexpr int NF0 = (NFRAG_ + 3) / 4, NF1 = (NFRAG_ - 2 * NF0) / 2;
   static_assert(2 * NF0 + 2 * NF1 == NFRAG_ && NF1 >= 1 && NB % 16 == 0, "fragment split");
-  static constexpr int NCW = 8, NPW = 4;        // consumer / producer warps
+  static constexpr int NCW = 8, NPW = NPW_;     // consumer / producer warps
   static constexpr int NT = 32 * (NCW + NPW);
   static constexpr int NCT = 32 * NCW, NPT = 32 * NPW;
   static constexpr int KC = KC_, NKQ = KC / 4;  // primitives per stage (<= 64: the streamer issues two rows per lane)
@@ -39,9 +41,14 @@ struct WsCfg {
   static constexpr size_t SMEM = sizeof(double) * (NS * (A_STAGE + B_STAGE) + NPART + TSLOTS * 4 * P) + 256;
   // registers per warpgroup (setmaxnreg): 232 for four fragments (160 accumulator registers), 184 for three or fewer; the
   // three budgets add up to the 3 x 168 of the launch
-  static constexpr int REG_CONS4 = NF0 >= 4 ? 232 : 184, REG_CONS3 = NF1 >= 4 ? 232 : 184;
-  static constexpr int REG_PROD = 504 - REG_CONS4 - REG_CONS3;
+  // three budgets add up to the 3 x 168 of the launch; with two producer warpgroups (512 threads) every warpgroup keeps the
+  // 128 registers of the launch (two fragments per consumer warp need no more)
+  static constexpr int REG_LAUNCH = 65536 / NT / 8 * 8;
+  static constexpr int REG_CONS4 = NPW_ > 4 ? REG_LAUNCH : (NF0 >= 4 ? 232 : 184);
+  static constexpr int REG_CONS3 = NPW_ > 4 ? REG_LAUNCH : (NF1 >= 4 ? 232 : 184);
+  static constexpr int REG_PROD = NPW_ > 4 ? REG_LAUNCH : 504 - REG_CONS4 - REG_CONS3;
   static_assert(REG_PROD >= 88 && REG_PROD % 8 == 0, "register budget of the producer warpgroup");
+  static_assert(NPW_ == 4 || (NPW_ == 8 && NF0 <= 2), "512-thread variant: at most two fragments per consumer warp");
 };
 
 // Per-stage header written by the producers, read by the consumers.
@@ -660,15 +667,16 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   fence_proxy_async();
   __syncthreads();
   // setmaxnreg works per warpgroup (4 warps): 128 x (232 + 184 + 88) = 64512 registers = 384 x 168, the launch figure
+  constexpr bool REBALANCE = C::REG_CONS4 != C::REG_LAUNCH || C::REG_PROD != C::REG_LAUNCH;
   if (tid >= C::NCT) {
-    if (C::REG_PROD <= 168) reg_dec<C::REG_PROD>(); else reg_inc<C::REG_PROD>();
+    if (REBALANCE) { if (C::REG_PROD <= C::REG_LAUNCH) reg_dec<C::REG_PROD>(); else reg_inc<C::REG_PROD>(); }
     if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
     else ws_generator<C>(p, S, tid - C::NCT - 32);
   } else if (tid < 128) {
-    reg_inc<C::REG_CONS4>();
+    if (REBALANCE) reg_inc<C::REG_CONS4>();
     ws_consumer<C, C::NF0>(p, S, tid);
   } else {
-    reg_inc<C::REG_CONS3>();
+    if (REBALANCE) reg_inc<C::REG_CONS3>();
     ws_consumer<C, C::NF1>(p, S, tid);
   }
 }

@@ -72,7 +72,7 @@ def test_cube_cell_grid_ragged(G, O):
     assert (ref["f"] == 0).any()
 
 
-@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12])
+@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12, 13])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_all_configs(G, O, cfg, variant):
     """24-atom def2-TZVP-shaped synthetic molecule through every block-synchronous and warp-specialised configuration
@@ -654,7 +654,7 @@ def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
 
 
 # ---- round 2: the multi-MO-block paths of the tensor-core kernels -------------------------------------------------------
-@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12])
+@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12, 13])
 @pytest.mark.parametrize("nmo", [113, 300])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
@@ -678,7 +678,7 @@ def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
     print(cfg, nmo, variant, c["nblk"], _compare_cube(got, ref))
 
 
-@pytest.mark.parametrize("cfg", [4, 6])
+@pytest.mark.parametrize("cfg", [4, 6, 13])
 def test_nci_and_points_multi_block(G, O, cfg):
     """NCIPLOT evaluation and a ragged point list with three MO blocks (classification identical, nuclei flagged)."""
     from critic2_b200 import drivers, synth
@@ -689,7 +689,7 @@ def test_nci_and_points_multi_block(G, O, cfg):
         fld = G.WfnField(f, st)
     finally:
         G.set_option("wfn_cfg", -1)
-    assert fld.config()["nblk"] == 3
+    assert fld.config()["nblk"] == (4 if cfg == 13 else 3)
     of = _ofield(O, f, st)
     x0, xmat, ns = drivers.nci_grid(st, nstep=(15, 13, 17))
     rrho, rgrad, _ = of.nci(x0, xmat, ns)

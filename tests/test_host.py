@@ -211,10 +211,11 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     assert [pick(n) for n in (9, 16, 17, 21, 24)] == [10, 10, 11, 11, 11]
     assert [pick(n) for n in (25, 48, 64)] == [8, 8, 8]
     assert [pick(n) for n in (65, 100, 112)] == [4, 4, 4]
-    assert [pick(n) for n in (113, 150, 192)] == [8, 8, 8]
+    assert [pick(n) for n in (113, 128)] == [8, 8]
+    assert [pick(n) for n in (129, 150, 192)] == [13, 13, 13]     # WS64g: 64-column blocks, seven generator warps
     assert [pick(n) for n in (193, 224)] == [4, 4]
-    assert pick(250) == 8
-    assert [pick(n) for n in (300, 780, 3120)] == [6, 6, 6]      # BASELINE configs 4 and 5
+    assert [pick(n) for n in (225, 256, 300, 320, 350)] == [13] * 5
+    assert [pick(n) for n in (330, 400, 780, 3120)] == [6, 6, 6, 6]      # incl. BASELINE configs 4 and 5
 
 
 def test_aimpac_wfn_round_trip(tmp_path):
