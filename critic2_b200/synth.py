@@ -20,8 +20,9 @@ _H_S = [34.0613410, 5.1235746, 1.1646626, 0.32723041, 0.10307241]
 _H_P = [0.8]
 
 
-def _atom_prims(z: int):
-    """[(itype, exponent)] for one atom."""
+def _atom_prims(z: int, gh: bool = False):
+    """[(itype, exponent)] for one atom.  gh: heavy atoms also get one g shell (types 21-35) and one h shell (36-56, the
+    largest angular momentum of calculate_mo_gto's type table, wfn_private@proc.F90:2695-2705)."""
     out = []
     if z == 1:
         out += [(1, a) for a in _H_S]
@@ -36,11 +37,14 @@ def _atom_prims(z: int):
         out += [(t, a * sc) for t in range(5, 11)]
     for a in _C_F:
         out += [(t, a * sc) for t in range(11, 21)]
+    if gh:
+        out += [(t, 1.011 * sc) for t in range(21, 36)]
+        out += [(t, 0.873 * sc) for t in range(36, 57)]
     return out
 
 
 def synthetic_molecule(lattice=(8, 8, 8), ndrop=12, composition=((6, 160), (7, 20), (8, 20), (1, 300)),
-                       seed=4, spacing=4.0, jitter=0.5, nmo=None, uhf=False, with_edf=False) -> Molwfn:
+                       seed=4, spacing=4.0, jitter=0.5, nmo=None, uhf=False, with_edf=False, gh=False) -> Molwfn:
     """Config 4 by default (500 atoms, 12 600 primitives, 780 MOs).  Config 5: lattice=(13,13,12), ndrop=28,
     composition=((6,640),(7,80),(8,80),(1,1200)), seed=5."""
     rng = np.random.default_rng(seed)
@@ -58,7 +62,7 @@ def synthetic_molecule(lattice=(8, 8, 8), ndrop=12, composition=((6, 160), (7, 2
     rng.shuffle(zs)
     icenter, itype, e = [], [], []
     for ia, z in enumerate(zs):
-        for t, a in _atom_prims(int(z)):
+        for t, a in _atom_prims(int(z), gh):
             icenter.append(ia + 1)
             itype.append(t)
             e.append(a)
@@ -97,7 +101,7 @@ def config5(seed=5) -> Molwfn:
                               composition=((6, 640), (7, 80), (8, 80), (1, 1200)), seed=seed)
 
 
-def small_synthetic(seed=11, uhf=False, with_edf=False, nmo=None) -> Molwfn:
+def small_synthetic(seed=11, uhf=False, with_edf=False, nmo=None, gh=False) -> Molwfn:
     """A 24-atom cousin of config 4 (3x3x3 lattice, 3 sites dropped) for parity tests the oracle finishes in seconds."""
     return synthetic_molecule(lattice=(3, 3, 3), ndrop=3, composition=((6, 7), (7, 2), (8, 2), (1, 13)), seed=seed,
-                              uhf=uhf, with_edf=with_edf, nmo=nmo)
+                              uhf=uhf, with_edf=with_edf, nmo=nmo, gh=gh)

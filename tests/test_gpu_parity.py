@@ -999,3 +999,28 @@ def test_warp_kernel_points_nder_nci_core_gkin_mo(G, O, cfg):
             fld.set_core(None)
     finally:
         G.set_option("wfn_cfg", -1)
+
+
+@pytest.mark.parametrize("cfg,nmo", [(9, 8), (11, 20), (8, 40), (4, 120), (6, 120), (13, 150)])
+def test_g_and_h_functions_through_every_kernel_family(G, O, cfg, nmo):
+    """Primitive types 21-56 (g and h shells: l = 4, 5 -- the top of calculate_mo_gto's type table,
+    wfn_private@proc.F90:2695-2705; powers up to x^7 in the second derivatives) through the warp, block-synchronous and
+    warp-specialised kernels: CUBE with all derivatives and a point list on the nuclei."""
+    from critic2_b200 import synth
+    f = synth.small_synthetic(nmo=nmo, gh=True)
+    assert f.itype.max() == 56
+    st = cases.mol_structure(f)
+    x0, xd, nn = cases.bbox_grid(st, (14, 12, 11), margin=2.5)
+    of = _ofield(O, f, st)
+    ref = of.cube(x0, xd, nn)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    assert fld.config()["cfg"] == cfg
+    print(cfg, nmo, _compare_cube(fld.cube(x0, xd, nn), ref))
+    pts = np.concatenate([st.r[:4], st.r[:4] + 0.37])
+    rres, res = of.grd_points(pts, 2, False), fld.points(pts, 2, False)
+    check_rho(res[:, 0], rres[:, 0])
+    check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])

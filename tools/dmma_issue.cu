@@ -28,6 +28,40 @@ __global__ void k(double* out, int iters, double a0, double b0) {
   for (int i = 0; i < NACC; i++) s += c[i][0] + c[i][1];
   out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
+// prefetch distance 2: the operand of group it+2 is loaded while group it issues
+template <int NACC>
+__global__ void k2(double* out, int iters, double a0, double b0) {
+  __shared__ double sm[2048];
+  for (int i = threadIdx.x; i < 2048; i += blockDim.x) sm[i] = a0 + i * 1e-9;
+  __syncthreads();
+  double c[NACC][2];
+#pragma unroll
+  for (int i = 0; i < NACC; i++) { c[i][0] = threadIdx.x; c[i][1] = i; }
+  int idx = threadIdx.x & 31;
+  double a = sm[idx], a1 = sm[idx + 32];
+  for (int it = 0; it < iters; it++) {
+    double a2 = sm[(idx + (it + 2) * 32) & 2047];
+#pragma unroll
+    for (int i = 0; i < NACC; i++) dmma884(c[i][0], c[i][1], a, b0);
+    a = a1; a1 = a2;
+  }
+  double s = 0;
+#pragma unroll
+  for (int i = 0; i < NACC; i++) s += c[i][0] + c[i][1];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+template <int NACC>
+void run2(double* out, int nsm, int threads) {
+  const int iters = 40000;
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int r = 0; r < 4; r++) {
+    cudaEventRecord(e0); k2<NACC><<<nsm, threads>>>(out, iters, 1.0000001, 1e-9); cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1); if (r && ms < best) best = ms;
+  }
+  printf("{\"warps_per_subpartition\":%d,\"nacc\":%d,\"lds\":2,\"tflops\":%.2f}\n", threads / 128, NACC,
+         2.0 * NACC * 256 * (double)iters * (threads / 32) * nsm / best / 1e9);
+}
 template <int NACC, bool LDS>
 void run(double* out, int nsm, int threads) {
   const int iters = 40000;
@@ -47,6 +81,7 @@ int main() {
     run<2, false>(out, p.multiProcessorCount, t); run<3, false>(out, p.multiProcessorCount, t);
     run<4, false>(out, p.multiProcessorCount, t); run<3, true>(out, p.multiProcessorCount, t);
     run<4, true>(out, p.multiProcessorCount, t); run<8, false>(out, p.multiProcessorCount, t);
+    run2<3>(out, p.multiProcessorCount, t); run2<4>(out, p.multiProcessorCount, t);
   }
   return 0;
 }
