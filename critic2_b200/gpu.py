@@ -337,6 +337,40 @@ class WfnField(_Field):
     def mo_points(self, pts, imo: int, periodic: bool = True):
         return self.mo_field(imo).values(pts, periodic)
 
+    # -- the spin and valence channels of rho2 (wfn_private@proc.F90:2091-2147, 2159-2200; grd :763-786) ---------------------
+    def channel(self, spin: int = 0, valence: bool = False) -> "WfnField":
+        """Companion field whose density is one channel of rho2: spin = 1 / 2 -> rho(2) / rho(3) (res%fspin, gfmodspin,
+        lapspin, gkinspin: the alpha / beta MOs of a UHF wavefunction plus HALF the EDF core, :2184-2198; half of everything
+        otherwise, :2159-2182); valence = True -> the channel without the EDF core (res%fval, gfmodval, del2fval and the
+        *spinval members).  Same kernels, same primitives: only the occupations and the EDF coefficients of the handle
+        differ, so every driver (CUBE, NCIPLOT, point lists, gkin) works on a channel.  Cached per (spin, valence)."""
+        import copy
+        from .wfn import WFN_UHF
+        if spin not in (0, 1, 2):
+            raise C2GpuError("channel: spin must be 0 (total), 1 (alpha) or 2 (beta)")
+        if spin == 0 and not valence:
+            return self
+        cache = self.__dict__.setdefault("_chan", {})
+        key = (spin, bool(valence))
+        if key not in cache:
+            f = self.f
+            g = copy.copy(f)
+            occ = np.array(f.occ, float)
+            if spin:
+                if f.wfntyp == WFN_UHF:
+                    alpha = np.arange(f.nmoocc) < f.nalpha           # imo <= nalpha, :2096
+                    occ = np.where(alpha if spin == 1 else ~alpha, occ, 0.0)
+                else:
+                    occ = 0.5 * occ                                   # rho(2) = rho(3) = rho(1) / 2, :2163-2164
+            g.occ = occ
+            if valence or f.nedf == 0:
+                g.icenter_edf, g.itype_edf = np.zeros(0, np.int32), np.zeros(0, np.int32)
+                g.e_edf, g.c_edf, g.dran_edf = np.zeros(0), np.zeros(0), np.zeros(0)
+            elif spin:
+                g.c_edf = 0.5 * np.asarray(f.c_edf, float)           # rho(2:3) += rhoc / 2, :2186
+            cache[key] = WfnField(g, self.st)
+        return cache[key]
+
     def config(self):
         a = np.zeros(8, np.int32)
         _check(lib().c2gpu_wfn_config(self.handle, _i(a)))

@@ -224,13 +224,21 @@ contains
   !> Returns c_null_ptr when the input is unsupported (STO basis, crystal environment): the caller keeps grd.
   !> With imo the handle holds that molecular orbital alone (nmoocc = 1, cmo = cmo(imo,:), occ = 1): the operand of
   !> c2gpu_eval_points_mo (calculate_mo, wfn_private@proc.F90:2447-2553; imo may address a virtual orbital).
-  function gpu_wfn_handle(w,c,imo) result(h)
-    use wfn_private, only: molwfn, wfn_frac
+  !> With spin = 1 / 2 and/or valence = .true. the handle is one channel of rho2 (wfn_private@proc.F90:2091-2147,
+  !> 2159-2200): the alpha / beta MOs of a UHF wavefunction plus half the EDF core (half of everything otherwise), and/or
+  !> the density without the EDF core -- the operand behind res%fspin, gfmodspin, lapspin, gkinspin and res%fval,
+  !> gfmodval, del2fval (fieldmod@proc.f90:763-786).  Only the occupations and EDF coefficients passed differ.
+  function gpu_wfn_handle(w,c,imo,spin,valence) result(h)
+    use wfn_private, only: molwfn, wfn_frac, wfn_uhf
     use crystalmod, only: crystal
     type(molwfn), intent(in), target :: w
     type(crystal), intent(in) :: c
     integer, intent(in), optional :: imo
+    integer, intent(in), optional :: spin
+    logical, intent(in), optional :: valence
     type(c_ptr) :: h
+    real(c_double), allocatable :: occ(:), cedf(:)
+    integer :: ispin, nedf
     real(c_double), allocatable :: row(:)
     real(c_double) :: one(1)
     real(c_double), allocatable :: xyz(:,:)
@@ -252,14 +260,39 @@ contains
        one = 1d0
        ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
           1_c_int,1_c_int,row,one,0_c_int,1_c_int,0_c_int,dumi,dumi,dumr,dumr,dumr,1_c_int,c%m_x2c,c%m_c2x,h)
-    else if (w%nedf > 0) then
-       ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
-          int(w%nmoocc,c_int),ldc,w%cmo,w%occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),int(w%nedf,c_int),&
-          w%icenter_edf,w%itype_edf,w%e_edf,w%c_edf,w%dran_edf,1_c_int,c%m_x2c,c%m_c2x,h)
     else
-       ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
-          int(w%nmoocc,c_int),ldc,w%cmo,w%occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),0_c_int,&
-          dumi,dumi,dumr,dumr,dumr,1_c_int,c%m_x2c,c%m_c2x,h)
+       ! occupations and EDF coefficients of the requested channel (total: as they are)
+       ispin = 0
+       if (present(spin)) ispin = spin
+       allocate(occ(w%nmoocc))
+       occ = w%occ(1:w%nmoocc)
+       nedf = w%nedf
+       if (present(valence)) then
+          if (valence) nedf = 0
+       end if
+       if (ispin == 1 .or. ispin == 2) then
+          if (w%wfntyp == wfn_uhf) then
+             if (ispin == 1) then
+                occ(w%nalpha+1:) = 0d0
+             else
+                occ(1:w%nalpha) = 0d0
+             end if
+          else
+             occ = 0.5d0 * occ
+          end if
+       end if
+       if (nedf > 0) then
+          allocate(cedf(nedf))
+          cedf = w%c_edf(1:nedf)
+          if (ispin == 1 .or. ispin == 2) cedf = 0.5d0 * cedf
+          ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
+             int(w%nmoocc,c_int),ldc,w%cmo,occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),int(nedf,c_int),&
+             w%icenter_edf,w%itype_edf,w%e_edf,cedf,w%dran_edf,1_c_int,c%m_x2c,c%m_c2x,h)
+       else
+          ierr = c2gpu_wfn_create(int(w%env%ncell,c_int),xyz,int(w%npri,c_int),w%icenter,w%itype,w%e,w%dran,&
+             int(w%nmoocc,c_int),ldc,w%cmo,occ,int(w%wfntyp,c_int),int(w%nalpha,c_int),0_c_int,&
+             dumi,dumi,dumr,dumr,dumr,1_c_int,c%m_x2c,c%m_c2x,h)
+       end if
     end if
     if (ierr == -1) h = c_null_ptr
     call gpu_check("gpu_wfn_handle",ierr)

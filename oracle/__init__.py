@@ -184,6 +184,17 @@ class Wfn:
             _d(_f64(f.occ)), f.wfntyp, f.nalpha, ne, _i(_i32(f.icenter_edf)) if ne else None,
             _i(_i32(f.itype_edf)) if ne else None, _d(_f64(f.e_edf)) if ne else None, _d(_f64(f.c_edf)) if ne else None)
 
+    def rho2(self, env: "Environ", x, nder=2):
+        """molwfn%rho2 at one Cartesian point: dict of rho(3), rhoval(3), grad(3,3), gradval(3,3), h(3,3,3), hval(3,3,3),
+        gkin(3), vir, stress(3,3) -- last index = total / alpha / beta (arrays indexed [spin][...])"""
+        out = np.zeros(91)
+        lib().orc_rho2(self.ptr, env.ptr, _d(_f64(x)), int(nder), _d(out))
+        F = lambda a, shp: np.asarray(a).reshape(shp[::-1]).transpose(*range(len(shp) - 1, -1, -1))   # Fortran order
+        return dict(rho=out[0:3].copy(), rhoval=out[3:6].copy(), grad=F(out[6:15], (3, 3)).T.copy(),
+                    gradval=F(out[15:24], (3, 3)).T.copy(), h=np.moveaxis(F(out[24:51], (3, 3, 3)), 2, 0).copy(),
+                    hval=np.moveaxis(F(out[51:78], (3, 3, 3)), 2, 0).copy(), gkin=out[78:81].copy(), vir=out[81],
+                    stress=F(out[82:91], (3, 3)).copy())
+
     def tables(self):
         f = self.f
         dran, spc = np.zeros(f.npri), np.zeros(f.natom)

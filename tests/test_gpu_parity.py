@@ -1024,3 +1024,42 @@ def test_g_and_h_functions_through_every_kernel_family(G, O, cfg, nmo):
     rres, res = of.grd_points(pts, 2, False), fld.points(pts, 2, False)
     check_rho(res[:, 0], rres[:, 0])
     check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])
+
+
+@pytest.mark.parametrize("uhf,cfg,nmo", [(True, -1, 20), (True, 6, 230), (False, -1, 20), (True, 8, 50)])
+def test_spin_and_valence_channels_of_rho2(G, O, uhf, cfg, nmo):
+    """res%fspin / gfmodspin / lapspin / gkinspin and res%fval / gfmodval / del2fval (+ *spinval) of grd for a wavefunction
+    field (fieldmod@proc.f90:763-786; rho2 wfn_private@proc.F90:2091-2147, 2159-2200): companion handles with masked
+    occupations and a scaled / removed EDF core, against the oracle's full rho2 output."""
+    from critic2_b200 import synth
+    f = synth.small_synthetic(uhf=uhf, with_edf=True, nmo=nmo)
+    st = cases.mol_structure(f)
+    env, w = O.Environ(st), O.Wfn(f)
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+        rng = np.random.default_rng(31)
+        heavy = st.r[f.z > 1][:4]
+        pts = np.concatenate([heavy + rng.normal(0, 0.15, heavy.shape), rng.uniform(st.r.min(0) - 2, st.r.max(0) + 2, (150, 3))])
+        ref = [w.rho2(env, x, 2) for x in pts]
+        assert max(abs(r["rho"][0] - r["rhoval"][0]) for r in ref) > 1e-3          # the EDF core really contributes
+        for spin in (0, 1, 2):
+            for val in (False, True):
+                ch = fld.channel(spin=spin, valence=val)
+                res = ch.points(pts, nder=2, periodic=False)
+                gk = ch.gkin_points(pts, periodic=False)
+                kr, kg, kh = ("rhoval", "gradval", "hval") if val else ("rho", "grad", "h")
+                rho = np.array([r[kr][spin] for r in ref])
+                grad = np.array([r[kg][spin] for r in ref])
+                hh = np.array([r[kh][spin].reshape(-1) for r in ref])
+                check_rho(res[:, 0], rho, f"rho spin {spin} val {val}")
+                check_vec(res[:, 1:4], grad, "grad", rho=rho)
+                check_vec(res[:, 4:13], hh, "hess", rho=rho)
+                lap = hh[:, 0] + hh[:, 4] + hh[:, 8]
+                hn = np.sqrt((hh ** 2).sum(1))
+                assert (np.abs(res[:, 14] - lap) / np.maximum(hn, 1e-4 * np.abs(rho))).max() <= cases.TOL_DER
+                gkr = np.array([r["gkin"][spin] for r in ref])                      # no core term in gkin
+                assert (np.abs(gk - gkr) / np.maximum(np.abs(gkr), 1e-30)).max() <= cases.TOL_DER
+        assert fld.channel() is fld and fld.channel(spin=1) is fld.channel(spin=1)
+    finally:
+        G.set_option("wfn_cfg", -1)
