@@ -326,8 +326,8 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
       size_t nt = (size_t)r.grid * 2 * r.acache_chunks;
       if (cudaMalloc(&d, nt * 5120 * sizeof(double)) == cudaSuccess) { r.allocs.push_back(d); r.acache = (double *)d; } else rc = 2;
       if (!rc && cudaMalloc(&d, nt * 8 * sizeof(int)) == cudaSuccess) { r.allocs.push_back(d); r.acache_nz = (int *)d; } else rc = 2;
-      size_t prim_cap = (size_t)((npri + 1) & ~1) + 64;
-      if (!rc && cudaMalloc(&d, (size_t)r.grid * prim_cap * 64) == cudaSuccess) { r.allocs.push_back(d); r.ws_rec = (double *)d; } else rc = 2;
+      size_t shell_cap = (size_t)((h->nshell + 3) & ~3);   // one 96-byte record per active shell of a sub-tile
+      if (!rc && cudaMalloc(&d, (size_t)r.grid * shell_cap * 96) == cudaSuccess) { r.allocs.push_back(d); r.ws_rec = (double *)d; } else rc = 2;
     }
     if (!rc && cudaStreamCreateWithFlags(&r.stream, cudaStreamNonBlocking) != cudaSuccess) rc = 2;
     if (rc) {

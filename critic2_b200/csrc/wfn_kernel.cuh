@@ -35,7 +35,7 @@ struct WfnParams {
   // warp-specialised kernel only: per-CTA cache of chi tiles in global memory (L2), re-used by MO blocks 1..nblk-1
   double *acache;       // [grid][2 tile parities][acache_chunks][A_STAGE]
   int *acache_nz;       // [grid][2][acache_chunks][8] k-quad masks
-  double *ws_rec;       // [grid][prim_cap][8] records of the active primitives of the current sub-tile
+  double *ws_rec;       // [grid][shell_cap][12] records of the active shells of the current sub-tile
   int acache_chunks;
   // value-only (ND = 1) launches only.  bits 0-1 = k in 1..3: the basis value is replaced by its k-th Cartesian derivative,
   // so the pass returns sum_mo occ (d_k phi)^2 -- three such passes give the kinetic energy density G = res%gkin

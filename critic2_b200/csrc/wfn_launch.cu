@@ -353,3 +353,15 @@ cudaError_t wfn_count_launch(const WfnDev &w, const GridDesc &g, const CellXf &x
 }
 
 }  // namespace c2
+
+#if C2_WS_DIAG & 16
+// development only (tools/ws_diag.sh): per (CTA, consumer warp) {cycles waiting for a full stage, cycles in the MMA loop,
+// DMMA warp instructions, cycles alive, wait at the first stage of a sub-tile, cycles in the block / sub-tile epilogues,
+// stages, sub-tiles} of the last wfn_ws_kernel launch on the current device
+extern "C" int c2gpu_ws_gdiag_read(unsigned long long *out, int n) {   // generator warps 0/1: {wait free, S2, chi, alive}
+  return cudaMemcpyFromSymbol(out, g_ws_gdiag, sizeof(unsigned long long) * (size_t)(n < 160 * 8 ? n : 160 * 8)) != cudaSuccess;
+}
+extern "C" int c2gpu_ws_diag_read(unsigned long long *out, int n) {
+  return cudaMemcpyFromSymbol(out, g_ws_diag, sizeof(unsigned long long) * (size_t)(n < 160 * 64 ? n : 160 * 64)) != cudaSuccess;
+}
+#endif

@@ -13,6 +13,21 @@
 #pragma once
 #include "wfn_kernel.cuh"
 
+// Development diagnostics (tools/ws_diag.sh builds separate libraries with -DC2_WS_DIAG=bits; the shipped library has 0 and
+// none of this code).  Results of a diagnostic build are NOT valid field values: the bits remove work to see what the
+// tensor pipe is waiting for.  1: the streamer issues no TMA copies (stages complete at once; consumers multiply stale
+// shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: the consumers keep their MMA
+// operands in registers (no shared-memory operand loads inside the loop).  16: consumer warps accumulate clock64() spent
+// waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
+// do not store the chi tiles.  64: no exp in the generators.
+#ifndef C2_WS_DIAG
+#define C2_WS_DIAG 0
+#endif
+#if C2_WS_DIAG & 16
+__device__ unsigned long long g_ws_diag[160 * 8 * 8];
+__device__ unsigned long long g_ws_gdiag[160 * 8];
+#endif
+
 namespace c2 {
 
 // NFRAG_ = 8-column fragments per MO block: 14 (NB = 112, large MO counts) or 8 (NB = 64, a few dozen to ~200 MOs, where
@@ -134,23 +149,105 @@ __device__ __forceinline__ void ws_prod_bbox(double lo[3], double hi[3], const W
 // Hand-over: ready[b] (generator -> streamer, tile in buffer b complete) and freeb[b] (streamer -> generator, every
 // TMA load of the tile in buffer b has landed), both single-arrival mbarriers used with the usual phase parity.
 // ---------------------------------------------------------------------------------------------------------------
+// Layout of one (k-quad, derivative row) slice of a chi tile: 4 primitives x 16 points.  Primitive-major, so the 16 points a
+// generator half-warp evaluates for one primitive are one 128-byte line of the chi-tile cache (point-major slices made every
+// store instruction touch 32 sectors, 8 bytes each: the generators were bound by the store path); the two 8-point row groups
+// swap places for odd k, so the consumers' A-fragment load (lane = (row, k): 8 rows x 4 primitives of one row group) reads
+// k = 0, 2 and k = 1, 3 from different bank halves: two conflict-free wavefronts, the minimum for 256 bytes.
+__device__ __forceinline__ int ws_a_index(int k, int pt) { return k * 16 + (pt ^ ((k & 1) << 3)); }
+
+// ---- chi of the primitives of ONE SHELL at one point (generator warps) ------------------------------------------------
+// The generators share the FP64 unit with the consumers' DMMAs and lose almost every arbitration (measured: ~170 cycles per
+// FP64 instruction while two consumer warps stream DMMAs), so what counts here is the NUMBER of FP64 instructions a warp
+// issues: everything common to the primitives of a shell -- displacement, squares, screen, exp, 2a, 2a x, (2a x)^2 -- is
+// computed once per (point, shell), and what depends on (lx, ly, lz) is picked with selects (integer pipe), which also keeps
+// the two half-warps (two shells) on one instruction stream.  Same formulas as axis_terms / prim_chi (wfn_device.cuh;
+// src/wfn_private@proc.F90:2755-2768): f0 = x^l, f1 = l x^(l-1) - 2a x^(l+1), f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + (2a x)^2 x^l.
+struct WsShellAxis {
+  double x, x2, twox, tx, tx2;   // displacement, its square, 2x, 2a x, (2a x)^2
+};
+__constant__ double c_ws_lf[8] = {0, 1, 2, 3, 4, 5, 6, 7};          // l
+__constant__ double c_ws_ll1[8] = {0, 0, 2, 6, 12, 20, 30, 42};     // l (l - 1)
+__constant__ double c_ws_2l1[8] = {1, 3, 5, 7, 9, 11, 13, 15};      // 2 l + 1
+
+// BIG = false: l <= 2 (s, p, d shells): no multiplication for the powers.  ta = 2a.
+template <int ND, bool BIG>
+__device__ __forceinline__ void ws_axis(const WsShellAxis &a, int l, double ta, double &f0, double &f1, double &f2) {
+  if (!BIG) {
+    f0 = l == 2 ? a.x2 : (l == 1 ? a.x : 1.0);
+    if (ND > 1) {
+      const double lpm1 = l == 2 ? a.twox : (l == 1 ? 1.0 : 0.0);   // l x^(l-1)
+      f1 = fma(-a.tx, f0, lpm1);
+      if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? 2.0 : 0.0);
+    }
+  } else {
+    const double x4 = a.x2 * a.x2;
+    const int n = l - 2;
+    const double pm2 = l >= 2 ? ((n & 1) ? a.x : 1.0) * ((n & 2) ? a.x2 : 1.0) * ((n & 4) ? x4 : 1.0) : 0.0;
+    const double pm1 = l >= 2 ? pm2 * a.x : (l == 1 ? 1.0 : 0.0);
+    f0 = l >= 1 ? pm1 * a.x : 1.0;
+    if (ND > 1) {
+      f1 = fma(-a.tx, f0, c_ws_lf[l & 7] * pm1);
+      if (ND > 4) f2 = fma(f0, fma(-c_ws_2l1[l & 7], ta, a.tx2), c_ws_ll1[l & 7] * pm2);
+    }
+  }
+}
+
+template <int ND, bool BIG>
+__device__ __forceinline__ void ws_shell_prim_chi(const WsShellAxis &ax, const WsShellAxis &ay, const WsShellAxis &az, int lx, int ly,
+                                                  int lz, double ta, double ex, int mode, double *chi) {
+  double x0, x1 = 0, x2 = 0, y0, y1 = 0, y2 = 0, z0, z1 = 0, z2 = 0;
+  if (ND == 1 && (mode & 3)) {   // value-only launches: the k-th Cartesian derivative as the "value" (WfnParams::chi_mode)
+    ws_axis<4, BIG>(ax, lx, ta, x0, x1, x2);
+    ws_axis<4, BIG>(ay, ly, ta, y0, y1, y2);
+    ws_axis<4, BIG>(az, lz, ta, z0, z1, z2);
+    const int k = mode & 3;
+    chi[0] = (k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1)) * ex;
+    return;
+  }
+  ws_axis<ND, BIG>(ax, lx, ta, x0, x1, x2);
+  ws_axis<ND, BIG>(ay, ly, ta, y0, y1, y2);
+  ws_axis<ND, BIG>(az, lz, ta, z0, z1, z2);
+  const double xe = x0 * ex, yz = y0 * z0;
+  chi[0] = xe * yz;
+  if (ND > 1) {
+    const double yze = yz * ex, xze = xe * z0, xye = xe * y0;
+    chi[ND > 1 ? 1 : 0] = x1 * yze;
+    chi[ND > 1 ? 2 : 0] = y1 * xze;
+    chi[ND > 1 ? 3 : 0] = z1 * xye;
+    if (ND > 4) {
+      const double ye = y0 * ex, ze = z0 * ex;
+      chi[ND > 4 ? 4 : 0] = x2 * yze;
+      chi[ND > 4 ? 5 : 0] = y2 * xze;
+      chi[ND > 4 ? 6 : 0] = z2 * xye;
+      chi[ND > 4 ? 7 : 0] = (x1 * y1) * ze;
+      chi[ND > 4 ? 8 : 0] = (x1 * z1) * ye;
+      chi[ND > 4 ? 9 : 0] = (z1 * y1) * xe;
+    }
+  }
+}
+
 template <class C>
 __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid) {
-  constexpr int ND = C::ND, P = C::P, KC = C::KC, NGW = C::NPW - 1, NGT = 32 * NGW, NGRP = NGT / 16;
+  constexpr int ND = C::ND, P = C::P, KC = C::KC, NGW = C::NPW - 1, NGT = 32 * NGW;
   const int lane = gtid & 31, warp = gtid >> 5;
-  const int grp = gtid >> 4;        // 16-lane group: one k-quad (4 primitives x 16 points) at a time
   const int pt = gtid & 15;
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
   // per-CTA scratch: shell list [shell_cap] then two (primitive, shell) lists [prim_cap] (one per cache buffer)
   int *sh_list = p.scratch + (size_t)blockIdx.x * (p.shell_cap + 4 * p.prim_cap);
   int2 *pr_list0 = reinterpret_cast<int2 *>(sh_list + p.shell_cap);
-  double *rec = p.ws_rec + (size_t)blockIdx.x * (size_t)p.prim_cap * 8;
+  constexpr int WS_REC = 12;   // doubles per active-shell record (96 bytes)
+  double *rec = p.ws_rec + (size_t)blockIdx.x * (size_t)p.shell_cap * WS_REC;
   const int na = grid_na(g), nb = grid_nb(g);
   const int npsuper = g.sa * g.sb * g.sc;
   const int nsub_a = g.sa / g.ta, nsub_b = g.sb / g.tb, nsub_c = g.sc / g.tc;
   unsigned tcount = 0;
   __shared__ int s_nuc_tmp[16];
+#if C2_WS_DIAG & 16
+  long long gg_free = 0, gg_s2 = 0, gg_chi = 0, gg_t0 = 0, gg_t1 = 0;
+  const long long gg_start = clock64();
+#endif
 
   for (;;) {
     if (gtid == 0) S.p_int[0] = atomicAdd(p.work_counter, 1);
@@ -240,9 +337,18 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
         ws_prod_bbox<C, NGW>(lo, hi, S, S.p_bb + 6, gtid);
       }
       // the streamer has finished with the tile that used this cache buffer (and its primitive list)
+#if C2_WS_DIAG & 16
+      gg_t0 = clock64();
+#endif
       mbar_wait(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
-      // ---- S2: refine against the sub-tile box, expand to (primitive, shell) pairs + 64-byte records (ordered) ------
-      int kact = 0;
+#if C2_WS_DIAG & 16
+      gg_t1 = clock64(); gg_free += gg_t1 - gg_t0;
+#endif
+      // ---- S2: refine against the sub-tile box; ordered expansion into (primitive, shell) pairs (the streamer's C-row
+      // gather) and one 96-byte record per ACTIVE SHELL: centre, exponent, dran, the two bounds of the rounding band of
+      // the screen, (first slot in the primitive list, primitive count) and the angular momenta of its primitives, so the
+      // evaluation below depends on ONE global load per shell ------------------------------------------------------------
+      int kact = 0, nact_sh = 0;
       for (int base = 0; base < ns; base += NGT) {
         int j = base + gtid, cnt = 0, pb = 0, s = 0;
         if (j < ns) {
@@ -253,7 +359,8 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
             cnt = w.shell_pbeg[s + 1] - pb;
           }
         }
-        int incl = cnt;
+        const int mine = cnt | (cnt > 0 ? 0x10000 : 0);   // packed: primitives (a batch has < 65536), shells
+        int incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
           int v = __shfl_up_sync(~0u, incl, o);
@@ -261,79 +368,123 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
         }
         if (lane == 31) S.p_cnt[warp] = incl;
         named_bar_sync(2, NGT);
-        int off = kact, tot = 0;
+        int offp = incl - mine, tot = 0;
 #pragma unroll
         for (int i = 0; i < NGW; i++) {
-          if (i < warp) off += S.p_cnt[i];
+          if (i < warp) offp += S.p_cnt[i];
           tot += S.p_cnt[i];
         }
-        off += incl - cnt;
         if (cnt > 0) {
+          const int off = kact + (offp & 0xffff);
           const double4 xa = w.shell_xa[s];
           const double2 cut = w.shell_cut[s];
+          unsigned long long lc[4] = {0ull, 0ull, 0ull, 0ull};   // (lx, ly, lz) of the primitives: 10 bits each, 6 per word
           for (int i = 0; i < cnt; i++) {
             pr_list[off + i] = make_int2(pb + i, s);
             const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[pb + i];
-            const long long bits = (long long)s | ((long long)l.x << 32) | ((long long)l.y << 40) | ((long long)l.z << 48);
-            double4 *r = reinterpret_cast<double4 *>(rec + (size_t)(off + i) * 8);
-            r[0] = xa;
-            r[1] = make_double4(cut.x, cut.y, __longlong_as_double(bits), 0.0);
+            lc[i / 6] |= (unsigned long long)(l.x | (l.y << 3) | (l.z << 6)) << (10 * (i % 6));
           }
+          const long long bits = (long long)off | ((long long)cnt << 24);
+          double4 *r = reinterpret_cast<double4 *>(rec + (size_t)(nact_sh + (offp >> 16)) * WS_REC);
+          r[0] = xa;
+          r[1] = make_double4(cut.x, cut.y * (1.0 - 1e-14), cut.y * (1.0 + 1e-14), __longlong_as_double(bits));
+          r[2] = make_double4(__longlong_as_double((long long)lc[0]), __longlong_as_double((long long)lc[1]),
+                              __longlong_as_double((long long)lc[2]), __longlong_as_double((long long)lc[3]));
         }
-        kact += tot;
+        kact += tot & 0xffff;
+        nact_sh += tot >> 16;
         named_bar_sync(2, NGT);
       }
-      __threadfence_block();
-      named_bar_sync(2, NGT);   // records visible to every generator thread
       const int nch = (kact + KC - 1) / KC;
-      const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
-      const bool pvalid = tp[3 * P + pt] != 0.0;
+      const int nquad = nch * (KC / 4);
       double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::ACHUNK;
       int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * 8;
-      // ---- chi tiles: k-quad q = (chunk, quad within the chunk) -> 16-lane group q % NGRP ------------------------------
-      const int nquad = nch * (KC / 4);
-      const int sbase = lane & 16;
-      int prev_sh = -1;
-      double dx = 0, dy = 0, dz = 0, ex = 0, al = 0;
-      bool pass = false;
-      for (int q = grp; q < nquad; q += NGRP) {
-        const double2 mine = reinterpret_cast<const double2 *>(rec + (size_t)q * 32)[pt];
-        double *Aq = agbase + (size_t)q * ND * P * 4 + pt * 4;   // quads are contiguous: chunk c starts at c * A_STAGE
-        unsigned nzbits = 0;
-#pragma unroll
-        for (int k4 = 0; k4 < 4; k4++) {
-          const int gk = q * 4 + k4;
-          const double rx = __shfl_sync(~0u, mine.x, sbase + k4 * 4), ry = __shfl_sync(~0u, mine.y, sbase + k4 * 4);
-          const double rz = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 1), ra = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 1);
-          const double rc = __shfl_sync(~0u, mine.x, sbase + k4 * 4 + 2), rc2 = __shfl_sync(~0u, mine.y, sbase + k4 * 4 + 2);
-          const long long bits = __double_as_longlong(__shfl_sync(~0u, mine.x, sbase + k4 * 4 + 3));
-          double chi[ND];
-#pragma unroll
-          for (int d = 0; d < ND; d++) chi[d] = 0.0;
-          if (gk < kact && pvalid) {
-            const int sh = (int)(bits & 0xffffffffll);
-            if (sh != prev_sh) {   // new shell: distance screen (:2747) and exponential (:2749) shared by its primitives
-              prev_sh = sh;
-              dx = px - rx; dy = py - ry; dz = pz - rz;
-              al = ra;
-              const double d2 = dx * dx + dy * dy + dz * dz;
-              pass = within_cut(dx, dy, dz, d2, rc, rc2);
-              ex = pass ? exp(-al * d2) : 0.0;
-            }
-            if (pass) {
-              prim_chi_mode<ND>(dx, dy, dz, (int)((bits >> 32) & 0xff), (int)((bits >> 40) & 0xff),
-                                (int)((bits >> 48) & 0xff), al, ex, p.chi_mode, chi);
-              nzbits |= 1u;
-            }
-          }
-          const int sw = k4 ^ ((pt >> 2) & 3);
-#pragma unroll
-          for (int d = 0; d < ND; d++) Aq[d * P * 4 + sw] = chi[d];
+      for (int q = gtid; q < nquad; q += NGT) nzbase[q] = 0;   // k-quad masks: OR-ed together below
+      __threadfence_block();
+      named_bar_sync(2, NGT);   // records and cleared masks visible to every generator thread
+      const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
+      const bool pvalid = tp[3 * P + pt] != 0.0;
+#if C2_WS_DIAG & 16
+      gg_t0 = clock64(); gg_s2 += gg_t0 - gg_t1;
+#endif
+      // ---- chi tiles: a warp takes two active shells at a time (half-warp = shell, lane = point) and walks their
+      // primitives together; slot k of the primitive list is column k % 4 of k-quad k / 4 (quads are contiguous in the
+      // cache: chunk c starts at c * A_STAGE) ---------------------------------------------------------------------------
+      const int hsh = lane & 16;
+      for (int j = warp; 2 * j < nact_sh; j += NGW) {
+        const int si = 2 * j + (hsh >> 4);
+        const bool has = si < nact_sh;
+        double4 xa = make_double4(0.0, 0.0, 0.0, 0.0), r1 = make_double4(0.0, 0.0, 0.0, 0.0), r2 = r1;
+        if (has) {
+          const double4 *r = reinterpret_cast<const double4 *>(rec + (size_t)si * WS_REC);
+          xa = r[0];
+          r1 = r[1];
+          r2 = r[2];
         }
-        const unsigned bal = __ballot_sync(~0u, nzbits != 0);
-        const unsigned half = (bal >> (lane & 16)) & 0xffffu;
-        if (pt == 0) nzbase[q] = ((half & 0xffu) ? 1 : 0) | ((half & 0xff00u) ? 2 : 0);
+        if (si + 2 * NGW < nact_sh) {   // the records of this half-warp's next shell: into L1 while this one is evaluated
+          const double *nx = rec + (size_t)(si + 2 * NGW) * WS_REC;
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(nx));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(nx + WS_REC - 1));
+        }
+        const long long bits = __double_as_longlong(r1.w);
+        const int off = (int)(bits & 0xffffff), cnt = (int)((bits >> 24) & 0xff);
+        const int cmax = max(cnt, __shfl_xor_sync(~0u, cnt, 16));
+        WsShellAxis ax, ay, az;
+        ax.x = px - xa.x; ay.x = py - xa.y; az.x = pz - xa.z;
+        ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x; az.x2 = az.x * az.x;
+        const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), az.x2);
+        bool pass = has && pvalid && !(d2 > r1.z);                          // screen (:2747): outside the rounding band ...
+        if (pass && !(d2 < r1.y)) pass = !(norm2_ref(ax.x, ay.x, az.x) > r1.x);   // ... inside it, the reference's own norm2
+        if (!__any_sync(~0u, pass)) {   // no point of the sub-tile within reach of either shell
+          for (int i = 0; i < cnt; i++) {
+            const int pos = off + i;
+            double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
+#pragma unroll
+            for (int d = 0; d < ND; d++) Aq[d * P * 4] = 0.0;
+          }
+          continue;
+        }
+        const double al = xa.w;
+        const double ex = pass ? ((C2_WS_DIAG & 64) ? 1.0 - al * d2 : exp(-al * d2)) : 0.0;   // :2749; 0 also zeroes every chi of the lane
+        const double ta = al + al;
+        ax.twox = ax.x + ax.x; ay.twox = ay.x + ay.x; az.twox = az.x + az.x;
+        ax.tx = ta * ax.x; ay.tx = ta * ay.x; az.tx = ta * az.x;
+        ax.tx2 = ax.tx * ax.tx; ay.tx2 = ay.tx * ay.tx; az.tx2 = az.tx * az.tx;
+        unsigned long long lw = (unsigned long long)__double_as_longlong(r2.x);
+        for (int i = 0; i < cmax; i++) {
+          const bool on = i < cnt;
+          const int lx = (int)(lw & 7u), ly = (int)((lw >> 3) & 7u), lz = (int)((lw >> 6) & 7u);
+          lw >>= 10;
+          if (i % 6 == 5) lw = (unsigned long long)__double_as_longlong(i < 6 ? r2.y : (i < 12 ? r2.z : r2.w));
+          double chi[ND];
+          if (C2_WS_DIAG & 2) {
+#pragma unroll
+            for (int d = 0; d < ND; d++) chi[d] = 0.0;
+          } else if (__any_sync(~0u, (lx | ly | lz) > 2))
+            ws_shell_prim_chi<ND, true>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+          else
+            ws_shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+          const int pos = off + i;
+          if (on && (!(C2_WS_DIAG & 32) || chi[0] == 1.2345)) {
+            double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
+#pragma unroll
+            for (int d = 0; d < ND; d++) Aq[d * P * 4] = chi[d];
+          }
+          const unsigned bal = __ballot_sync(~0u, on && pass);
+          const unsigned hm = (bal >> hsh) & 0xffffu;
+          if (pt == 0 && hm) atomicOr(&nzbase[pos >> 2], ((hm & 0xffu) ? 1 : 0) | ((hm & 0xff00u) ? 2 : 0));
+        }
       }
+      // unused columns of the last k-quad: zeros (their C rows are whatever the stage held before)
+      if (warp == 0)
+        for (int pos = kact + (hsh >> 4); pos < ((kact + 3) & ~3); pos += 2) {
+          double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
+#pragma unroll
+          for (int d = 0; d < ND; d++) Aq[d * P * 4] = 0.0;
+        }
+#if C2_WS_DIAG & 16
+      gg_chi += clock64() - gg_t0;
+#endif
       // tile complete: make the generic-proxy global writes visible to the streamer's bulk (async-proxy) loads
       __threadfence();
       fence_proxy_async_global();
@@ -346,6 +497,13 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       tcount++;
     }
   }
+#if C2_WS_DIAG & 16
+  if (lane == 0 && blockIdx.x < 160) {
+    unsigned long long *o = g_ws_gdiag + (size_t)blockIdx.x * 8;
+    if (warp == 0) { o[0] = gg_free; o[1] = gg_s2; o[2] = gg_chi; o[3] = clock64() - gg_start; }
+    if (warp == 1) { o[4] = gg_free; o[5] = gg_s2; o[6] = gg_chi; o[7] = clock64() - gg_start; }
+  }
+#endif
   if (gtid == 0) {   // exit descriptor
     const int buf = tcount & 1;
     mbar_wait(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
@@ -404,11 +562,16 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
           }
           __syncwarp();
           if (lane == 0) {
+#if C2_WS_DIAG & 1
+            mbar_expect_tx(&S.full[stg], 0u);
+#else
             mbar_expect_tx(&S.full[stg], (uint32_t)(nrow * NB * sizeof(double)) + (uint32_t)(C::A_STAGE * sizeof(double)));
             tma_bulk_g2s(S.As + stg * C::A_STAGE, agbase + (size_t)c * C::A_STAGE, (uint32_t)(C::A_STAGE * sizeof(double)),
                          &S.full[stg]);
+#endif
           }
           __syncwarp();
+          if (C2_WS_DIAG & 1) { it++; continue; }
           if (lane < nrow)
             tma_bulk_g2s(S.Bs + stg * C::B_STAGE + lane * SB, w.cmoT + (size_t)prim * w.ldc + (size_t)blk * NB,
                          (uint32_t)(NB * sizeof(double)), &S.full[stg]);
@@ -465,11 +628,11 @@ __device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const 
     kqm &= kqm - 1;
     double bn[NF];
 #pragma unroll
-    for (int ni = 0; ni < NF; ni++) bn[ni] = Bst[kqn * 4 * SB + ni * 8];
+    for (int ni = 0; ni < NF; ni++) bn[ni] = (C2_WS_DIAG & 4) ? b[ni] : Bst[kqn * 4 * SB + ni * 8];
     const double *An = Ast + (size_t)kqn * ND * P * 4;
 #pragma unroll
     for (int d = 0; d < ND; d++) {
-      const double an = (d + 1 < ND) ? Ak[(d + 1) * P * 4] : An[0];
+      const double an = (C2_WS_DIAG & 4) ? a : (d + 1 < ND) ? Ak[(d + 1) * P * 4] : An[0];
 #pragma unroll
       for (int ni = 0; ni < NF; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
       a = an;
@@ -488,7 +651,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
   const int wm = cw & 1, wn = cw >> 1;                 // row group (8 points) and warp column (0..3)
   const int f0 = wn < 2 ? wn * C::NF0 : 2 * C::NF0 + (wn - 2) * C::NF1;   // first fragment of this warp (4,4,3,3 for NB = 112)
   const int row = lane >> 2;
-  const int aoff = row * 4 + ((lane & 3) ^ (((wm * 8 + row) >> 2) & 3));
+  const int aoff = ws_a_index(lane & 3, wm * 8 + row);
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
   double acc[ND][NF][2];
@@ -500,21 +663,45 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     for (int ni = 0; ni < NF; ni++) acc[d][ni][0] = acc[d][ni][1] = 0.0;
   }
   unsigned tpar = 0;                                    // sub-tile parity: s_part is double-buffered
+#if C2_WS_DIAG & 16
+  long long dg_wait = 0, dg_mma = 0, dg_wait1 = 0, dg_epi = 0, dg_epi0 = 0;
+  unsigned long long dg_cnt = 0, dg_stages = 0, dg_tiles = 0;
+  const long long dg_start = clock64();
+#endif
 
   for (unsigned it = 0;; it++) {
     const int stg = it % NS;
+#if C2_WS_DIAG & 16
+    const long long dg0 = clock64();
+    if (dg_epi0) { dg_epi += dg0 - dg_epi0; dg_epi0 = 0; }
+#endif
     mbar_wait(&S.full[stg], (it / NS) & 1u);
+#if C2_WS_DIAG & 16
+    const long long dg1 = clock64();
+    dg_wait += dg1 - dg0;
+#endif
     const WsStageHdr &h = S.hdr[stg];
     const int flags = h.flags, blk = h.blk, tslot = h.tslot;
     if (flags & 16) break;
+#if C2_WS_DIAG & 16
+    dg_stages++;
+    if ((flags & 1) && blk == 0) { dg_wait1 += dg1 - dg0; dg_tiles++; }
+#endif
     if (!(flags & 8)) {
-      const double *Ast = S.As + stg * C::A_STAGE + (size_t)wm * 32 + aoff;
+      const double *Ast = S.As + stg * C::A_STAGE + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
       ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+#if C2_WS_DIAG & 16
+      dg_mma += clock64() - dg1;
+      dg_cnt += (unsigned long long)__popc((unsigned)h.kqmask[wm]) * ND * NF;
+#endif
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&S.empty[stg]);           // stage (and its header) no longer needed by this warp
     if (!(flags & 2)) continue;
+#if C2_WS_DIAG & 16
+    dg_epi0 = clock64();
+#endif
 
     // ---- end of an MO block: occupation-weighted quadratic forms of this thread's MOs (:2091-2147).  No barrier:
     // the partial sums stay in registers until the end of the sub-tile, so the warps drift apart and one warp's
@@ -635,6 +822,14 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     }
     if (w.nedf > 0) named_bar_sync(1, NCT);              // EDF scratch (the other s_part buffer) free again
   }
+#if C2_WS_DIAG & 16
+  if (lane == 0 && blockIdx.x < 160) {
+    unsigned long long *o = g_ws_diag + ((size_t)blockIdx.x * 8 + cw) * 8;
+    o[0] = (unsigned long long)dg_wait; o[1] = (unsigned long long)dg_mma; o[2] = dg_cnt;
+    o[3] = (unsigned long long)(clock64() - dg_start);
+    o[4] = (unsigned long long)dg_wait1; o[5] = (unsigned long long)dg_epi; o[6] = dg_stages; o[7] = dg_tiles;
+  }
+#endif
 }
 
 template <class C>
@@ -654,7 +849,11 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   S.full = s_full; S.empty = s_empty; S.hdr = s_hdr; S.tinfo = s_tinfo;
   S.p_red = s_pred; S.p_bb = s_pbb; S.p_cnt = s_pcnt; S.p_int = s_pint;
   S.ready = s_ready; S.freeb = s_freeb; S.tdesc = s_tdesc;
+#if C2_WS_DIAG & 8
+  const int tid = (threadIdx.x + C::NCT) % C::NT;   // producer warps get the lowest warp ids
+#else
   const int tid = threadIdx.x;
+#endif
   if (tid == 0) {
     for (int s = 0; s < C::NS; s++) {
       mbar_init(&s_full[s], 1);            // the streamer's arrive.expect_tx (+ the TMA byte count)

@@ -47,4 +47,29 @@ for cfg in [int(c) for c in a.cfgs.split(",")]:
               f"cfg {cfg} {fld.config()} slab [{a.z0},{a.z1}) {npts} pts mean n_act {nact / npts:.1f} "
               f"{ms:.1f} ms -> {npts / ms * 1e3:.3e} pts/s, {flops / ms / 1e9:.2f} TFLOP/s algorithmic "
               f"({flops / ms / 1e9 / 37.1 * 100:.1f}% of 37.1)", flush=True)
+    L = gpu.lib()
+    if hasattr(L, "c2gpu_ws_diag_read") and cfg in (6, 12, 13):   # diagnostic build (tools/ws_diag.sh, bit 16)
+        import ctypes as C
+        nsm = torch.cuda.get_device_properties(0).multi_processor_count
+        buf = (C.c_ulonglong * (nsm * 64))()
+        L.c2gpu_ws_diag_read(buf, nsm * 64)
+        d = np.frombuffer(buf, dtype=np.uint64).reshape(nsm, 8, 8).astype(np.float64)
+        for name, sl in (("4-fragment warps", slice(0, 4)), ("3-fragment warps", slice(4, 8))):
+            w_, m_, n_, t_, w1_, ep_, st_, ti_ = (d[:, sl, k] for k in range(8))
+            print(f"  {name}: of the alive cycles: wait at a sub-tile's first stage {100 * (w1_ / t_).mean():.2f} %, other waits "
+                  f"{100 * ((w_ - w1_) / t_).mean():.2f} %, block/sub-tile epilogues {100 * (ep_ / t_).mean():.2f} %, rest (stage "
+                  f"hand-over) {100 * ((t_ - w_ - m_ - ep_) / t_).mean():.2f} % = {((t_ - w_ - m_ - ep_) / st_).mean():.0f} cycles per stage; "
+                  f"{st_.mean():.0f} stages, {ti_.mean():.0f} sub-tiles, loop cycles per stage {(m_ / st_).mean():.0f}")
+            print(f"  {name}: waiting for a full stage {100 * (w_ / t_).mean():.1f} % (by sub-partition "
+                  f"{[round(100 * (w_ / t_)[:, j].mean(), 1) for j in range(4)]}), in the MMA loop {100 * (m_ / t_).mean():.1f} %, "
+                  f"DMMA x 16 clk / loop cycles {100 * (16 * n_ / m_).mean():.1f} %, / alive cycles {100 * (16 * n_ / t_).mean():.1f} %")
+        tot = 16 * (d[:, :4, 2] + d[:, 4:, 2]) / np.maximum(d[:, :4, 3], d[:, 4:, 3])
+        print(f"  DMMA pipe cycles per sub-partition / alive cycles: {100 * tot.mean():.1f} % (by sub-partition "
+              f"{[round(100 * tot[:, j].mean(), 1) for j in range(4)]})")
+    if hasattr(L, "c2gpu_ws_gdiag_read") and cfg in (6, 12, 13):
+        gb = (C.c_ulonglong * (nsm * 8))()
+        L.c2gpu_ws_gdiag_read(gb, nsm * 8)
+        gd = np.frombuffer(gb, dtype=np.uint64).reshape(nsm, 2, 4).astype(np.float64)
+        print(f"  generator warps 0/1: waiting for a free cache buffer {100 * (gd[:, :, 0] / gd[:, :, 3]).mean():.1f} %, S2 + records "
+              f"{100 * (gd[:, :, 1] / gd[:, :, 3]).mean():.1f} %, chi tiles {100 * (gd[:, :, 2] / gd[:, :, 3]).mean():.1f} % of their cycles")
     fld.close()
