@@ -124,20 +124,18 @@ int wfn_choose_config(int nmo, int force) {
   // up to 24 MOs: the warp-autonomous kernel (wfn_warp_kernel.cuh).  Measured on BASELINE config 1 (h2o-aqz 128^3, 5 MOs):
   // 1.17 ms against 1.46 ms for S1; config 2 (benzene-adz NCIPLOT 200^3, 21 MOs): 13.4 ms against 17.3 ms for S3w
   if (nfrag <= 3) return 8 + nfrag;
-  // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms): M2 54 per 64-column block, L 97 per 112-column
-  // block, the warp-specialised kernel 96 + 52 per 112-column block (its generators run ahead and the chi tiles are
-  // re-used from the L2 cache, which only pays from three blocks up).  tools/probe_mid.py reproduces the table:
-  //   nmo     48    100   128   150   192   224   | 780 (cfg 4, 500 atoms): WS 88 % of the DMMA peak, L 62 %
-  //   M2      57    111   111   164   164   217
-  //   L      103    103   197   197   197   197
-  //   WS     148    148   200   200   200   200
-  // L1 is L with 8-point sub-tiles and two CTAs per SM (224 threads each): 100.7 / 194.3 ms where L takes 103.2 / 197.9.
-  // WS64g (id 13: 64-column blocks, seven generator warps; same molecule, profiles/r2_probe_mid.log):
-  //   blocks   1     2     3     4     5      -> 92.6  119.5  157.4  198.2  239.7 ms: generator-bound up to two blocks, then
-  //   35 + 41 per block; it wins for 129-192, 225-320 and 337-384 MOs (256 MOs: 198 against 222 ms for M2, 67.9 % of the peak)
+  // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms; tools/probe_mid.py, profiles/r2_probe_mid.log):
+  //   blocks          1      2      3      4      5
+  //   M2    (64)     57.9  112.4  166.8  221.5  275.9    54.5 per block + 3
+  //   L1    (112)   102.5  198.3  294.2                  96 per block + 6
+  //   WS    (112)   144.4  195.4  246.2                  93.6 + 50.9 per block (generators ahead, chi tiles re-used from L2)
+  //   WS64g (64)     68.7   98.8  142.0  185.6  229.4    generator-bound for one block, then 11 + 43.7 per block
+  // (before the shell-wise generators WS64g took 92.6 / 119.5 / 157.4 / 198.2 / 239.7 and WS 154 / 207 / 259.)  WS64g now wins
+  // from 65 to ~400 MOs (128 MOs: 98.8 against 112.4 ms = 69 % of the DMMA peak, 192: 71 %, 256: 72.5 %); 500-atom config 4
+  // (780 MOs): WS 89.6 % of the peak, L 62 %.
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
-  const int tM = 54 * bM + 3, tL = 95 * bL + 6, tW = 96 + 52 * bL;
-  const int tG = bM <= 1 ? 93 : (bM == 2 ? 120 : 35 + 41 * bM);
+  const double tM = 54.5 * bM + 3, tL = 96 * bL + 6, tW = 93.6 + 50.9 * bL;
+  const double tG = bM <= 1 ? 68.7 : (bM == 2 ? 98.8 : 11 + 43.7 * bM);
   if (tG < tM && tG < tL && tG < tW) return 13;
   if (tM <= tL && tM <= tW) return 8;
   return tL <= tW ? 4 : 6;

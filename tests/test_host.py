@@ -202,7 +202,7 @@ def test_chk_nci_checkpoint_round_trip(tmp_path, monkeypatch):
 
 def test_kernel_configuration_choice_follows_the_measured_cost_model():
     """wfn_choose_config (no device needed): the warp kernel with 1 / 2 / 3 column fragments up to 24 MOs, then the cheapest of M2 (64-column blocks, two CTAs
-    per SM), L1 (112-column blocks, two CTAs per SM) and the warp-specialised kernel by the measured per-block costs (csrc/wfn_launch.cu)."""
+    per SM), L1 (112-column blocks, two CTAs per SM) and the two warp-specialised kernels by the measured per-block costs (csrc/wfn_launch.cu)."""
     import ctypes as C
     from critic2_b200 import gpu
     L = C.CDLL(gpu.LIB_PATH)
@@ -210,11 +210,8 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     assert [pick(n) for n in (1, 5, 8)] == [9, 9, 9]
     assert [pick(n) for n in (9, 16, 17, 21, 24)] == [10, 10, 11, 11, 11]
     assert [pick(n) for n in (25, 48, 64)] == [8, 8, 8]
-    assert [pick(n) for n in (65, 100, 112)] == [4, 4, 4]
-    assert [pick(n) for n in (113, 128)] == [8, 8]
-    assert [pick(n) for n in (129, 150, 192)] == [13, 13, 13]     # WS64g: 64-column blocks, seven generator warps
-    assert [pick(n) for n in (193, 224)] == [4, 4]
-    assert [pick(n) for n in (225, 256, 300, 320, 350)] == [13] * 5
+    # WS64g (64-column blocks, seven generator warps) from 65 MOs on since its generators evaluate shell-wise
+    assert [pick(n) for n in (65, 100, 112, 113, 128, 129, 150, 192, 193, 224, 225, 256, 300, 320, 350)] == [13] * 15
     assert [pick(n) for n in (330, 400, 780, 3120)] == [6, 6, 6, 6]      # incl. BASELINE configs 4 and 5
 
 
