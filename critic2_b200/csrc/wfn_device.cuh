@@ -84,6 +84,79 @@ __device__ __forceinline__ void prim_chi(double x, double y, double z, int lx, i
   }
 }
 
+// ---- chi of the primitives of ONE SHELL at one point -----------------------------------------------------------------
+// The generator warps of wfn_ws_kernel.cuh share the FP64 unit with the consumers' DMMAs and lose almost every
+// arbitration (tools/fp64_share.cu: 2500-9700 cycles per DFMA next to two DMMA-streaming warps), and the warp-autonomous
+// kernel's FP64 ALU work shares the unit with its own DMMAs: what counts is the NUMBER of FP64 instructions a warp issues.
+// Everything common to the primitives of a shell -- displacement, squares, 2a, 2a x, (2a x)^2 (and, in the generators,
+// screen and exp) -- is computed once per (point, shell); what depends on (lx, ly, lz) is picked with selects (integer
+// pipe), which also keeps lanes with different angular momenta on one instruction stream.  Same formulas as axis_terms /
+// prim_chi above (src/wfn_private@proc.F90:2755-2768): f0 = x^l, f1 = l x^(l-1) - 2a x^(l+1),
+// f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + (2a x)^2 x^l; 29 FP64 instructions per primitive for l <= 2 (a branch-free prim_chi: 65).
+struct ShellAxis {
+  double x, x2, twox, tx, tx2;   // displacement, its square, 2x, 2a x, (2a x)^2
+};
+static __constant__ double c_sh_lf[8] = {0, 1, 2, 3, 4, 5, 6, 7};          // l
+static __constant__ double c_sh_ll1[8] = {0, 0, 2, 6, 12, 20, 30, 42};     // l (l - 1)
+static __constant__ double c_sh_2l1[8] = {1, 3, 5, 7, 9, 11, 13, 15};      // 2 l + 1
+
+// BIG = false: l <= 2 (s, p, d shells): no multiplication for the powers.  ta = 2a.
+template <int ND, bool BIG>
+__device__ __forceinline__ void shell_axis(const ShellAxis &a, int l, double ta, double &f0, double &f1, double &f2) {
+  if (!BIG) {
+    f0 = l == 2 ? a.x2 : (l == 1 ? a.x : 1.0);
+    if (ND > 1) {
+      const double lpm1 = l == 2 ? a.twox : (l == 1 ? 1.0 : 0.0);   // l x^(l-1)
+      f1 = fma(-a.tx, f0, lpm1);
+      if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? 2.0 : 0.0);
+    }
+  } else {
+    const double x4 = a.x2 * a.x2;
+    const int n = l - 2;
+    const double pm2 = l >= 2 ? ((n & 1) ? a.x : 1.0) * ((n & 2) ? a.x2 : 1.0) * ((n & 4) ? x4 : 1.0) : 0.0;
+    const double pm1 = l >= 2 ? pm2 * a.x : (l == 1 ? 1.0 : 0.0);
+    f0 = l >= 1 ? pm1 * a.x : 1.0;
+    if (ND > 1) {
+      f1 = fma(-a.tx, f0, c_sh_lf[l & 7] * pm1);
+      if (ND > 4) f2 = fma(f0, fma(-c_sh_2l1[l & 7], ta, a.tx2), c_sh_ll1[l & 7] * pm2);
+    }
+  }
+}
+
+template <int ND, bool BIG>
+__device__ __forceinline__ void shell_prim_chi(const ShellAxis &ax, const ShellAxis &ay, const ShellAxis &az, int lx, int ly,
+                                                  int lz, double ta, double ex, int mode, double *chi) {
+  double x0, x1 = 0, x2 = 0, y0, y1 = 0, y2 = 0, z0, z1 = 0, z2 = 0;
+  if (ND == 1 && (mode & 3)) {   // value-only launches: the k-th Cartesian derivative as the "value" (WfnParams::chi_mode)
+    shell_axis<4, BIG>(ax, lx, ta, x0, x1, x2);
+    shell_axis<4, BIG>(ay, ly, ta, y0, y1, y2);
+    shell_axis<4, BIG>(az, lz, ta, z0, z1, z2);
+    const int k = mode & 3;
+    chi[0] = (k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1)) * ex;
+    return;
+  }
+  shell_axis<ND, BIG>(ax, lx, ta, x0, x1, x2);
+  shell_axis<ND, BIG>(ay, ly, ta, y0, y1, y2);
+  shell_axis<ND, BIG>(az, lz, ta, z0, z1, z2);
+  const double xe = x0 * ex, yz = y0 * z0;
+  chi[0] = xe * yz;
+  if (ND > 1) {
+    const double yze = yz * ex, xze = xe * z0, xye = xe * y0;
+    chi[ND > 1 ? 1 : 0] = x1 * yze;
+    chi[ND > 1 ? 2 : 0] = y1 * xze;
+    chi[ND > 1 ? 3 : 0] = z1 * xye;
+    if (ND > 4) {
+      const double ye = y0 * ex, ze = z0 * ex;
+      chi[ND > 4 ? 4 : 0] = x2 * yze;
+      chi[ND > 4 ? 5 : 0] = y2 * xze;
+      chi[ND > 4 ? 6 : 0] = z2 * xye;
+      chi[ND > 4 ? 7 : 0] = (x1 * y1) * ze;
+      chi[ND > 4 ? 8 : 0] = (x1 * z1) * ye;
+      chi[ND > 4 ? 9 : 0] = (z1 * y1) * xe;
+    }
+  }
+}
+
 // prim_chi with WfnParams::chi_mode: in value-only launches bits 0-1 select a Cartesian derivative as the "value"
 template <int ND>
 __device__ __forceinline__ void prim_chi_mode(double x, double y, double z, int lx, int ly, int lz, double al, double ex,

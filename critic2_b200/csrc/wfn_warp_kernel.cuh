@@ -32,65 +32,6 @@ struct WarpCfg {
 };
 
 #ifdef __CUDACC__
-// x^n for n = 0..7 without branches (lanes of a warp hold primitives of different angular momenta)
-__device__ __forceinline__ double pow_sel(double x, double x2, double x4, int n) {
-  return ((n & 1) ? x : 1.0) * ((n & 2) ? x2 : 1.0) * ((n & 4) ? x4 : 1.0);
-}
-
-// One Cartesian axis of a primitive (:2755-2766), branch-free version of axis_terms: f0 = x^l,
-// f1 = l x^(l-1) - 2a x^(l+1), f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + 4a^2 x^(l+2)
-template <int ND>
-__device__ __forceinline__ void axis_terms_bf(double x, int l, double al, double &f0, double &f1, double &f2) {
-  const double x2 = x * x, x4 = x2 * x2;
-  if (ND == 1) { f0 = pow_sel(x, x2, x4, l); return; }
-  if (ND == 4) {
-    const double xm1 = l >= 1 ? pow_sel(x, x2, x4, l - 1) : 0.0;
-    f0 = l >= 1 ? xm1 * x : 1.0;
-    f1 = (double)l * xm1 - 2.0 * al * (f0 * x);
-    return;
-  }
-  const double xm2 = l >= 2 ? pow_sel(x, x2, x4, l - 2) : 0.0;
-  const double xm1 = l >= 2 ? xm2 * x : (l == 1 ? 1.0 : 0.0);
-  f0 = l >= 1 ? xm1 * x : 1.0;
-  const double xp1 = f0 * x, ta = 2.0 * al;
-  f1 = (double)l * xm1 - ta * xp1;
-  f2 = (double)(l * (l - 1)) * xm2 - ta * (double)(2 * l + 1) * f0 + ta * ta * (xp1 * x);
-}
-
-template <int ND>
-__device__ __forceinline__ void prim_chi_bf(double x, double y, double z, int lx, int ly, int lz, double al, double ex,
-                                            int mode, double *chi) {
-  if (ND == 1 && (mode & 3)) {   // value-only launches: the k-th Cartesian derivative as the "value" (WfnParams::chi_mode)
-    double x0, x1, y0, y1, z0, z1, u;
-    axis_terms_bf<4>(x, lx, al, x0, x1, u);
-    axis_terms_bf<4>(y, ly, al, y0, y1, u);
-    axis_terms_bf<4>(z, lz, al, z0, z1, u);
-    const int k = mode & 3;
-    chi[0] = (k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1)) * ex;
-    return;
-  }
-  double x0, x1 = 0, x2 = 0, y0, y1 = 0, y2 = 0, z0, z1 = 0, z2 = 0;
-  axis_terms_bf<ND>(x, lx, al, x0, x1, x2);
-  axis_terms_bf<ND>(y, ly, al, y0, y1, y2);
-  axis_terms_bf<ND>(z, lz, al, z0, z1, z2);
-  const double xe = x0 * ex, ye = y0 * ex;
-  chi[0] = xe * y0 * z0;
-  if (ND > 1) {
-    const double yz = y0 * z0;
-    chi[ND > 1 ? 1 : 0] = x1 * yz * ex;
-    chi[ND > 1 ? 2 : 0] = y1 * xe * z0;
-    chi[ND > 1 ? 3 : 0] = z1 * xe * y0;
-    if (ND > 4) {
-      chi[ND > 4 ? 4 : 0] = x2 * yz * ex;
-      chi[ND > 4 ? 5 : 0] = y2 * z0 * xe;
-      chi[ND > 4 ? 6 : 0] = z2 * xe * y0;
-      chi[ND > 4 ? 7 : 0] = x1 * y1 * z0 * ex;
-      chi[ND > 4 ? 8 : 0] = x1 * z1 * ye;
-      chi[ND > 4 ? 9 : 0] = z1 * y1 * xe;
-    }
-  }
-}
-
 template <class C>
 __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_warp_kernel(const __grid_constant__ WfnParams p) {
   constexpr int ND = C::ND, NF = C::NF, NT = C::NT, NW = C::NW, LCAP = C::LCAP;
@@ -248,14 +189,22 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_warp_kernel(const __grid_c
 #pragma unroll
           for (int d = 0; d < ND; d++) chi[d] = 0.0;
           bool nz = false;
+          const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[prim];
+          const bool big = __any_sync(~0u, real && (l.x | l.y | l.z) > 2);   // f shells and up: powers by multiplication
           if (real && valid) {
             const double4 xa = w.shell_xa[e.y];
             const double2 cut = w.shell_cut[e.y];
-            const double dx = px - xa.x, dy = py - xa.y, dz = pz - xa.z;
-            const double d2 = dx * dx + dy * dy + dz * dz;
-            if (within_cut(dx, dy, dz, d2, cut.x, cut.y)) {                       // :2747
-              const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[prim];
-              prim_chi_bf<ND>(dx, dy, dz, l.x, l.y, l.z, xa.w, exp(-xa.w * d2), p.chi_mode, chi);   // :2749-2768
+            ShellAxis ax, ay, az;
+            ax.x = px - xa.x; ay.x = py - xa.y; az.x = pz - xa.z;
+            ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x; az.x2 = az.x * az.x;
+            const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), az.x2);
+            if (within_cut(ax.x, ay.x, az.x, d2, cut.x, cut.y)) {                 // :2747
+              const double ta = xa.w + xa.w, ex = exp(-xa.w * d2);                // :2749
+              ax.twox = ax.x + ax.x; ay.twox = ay.x + ay.x; az.twox = az.x + az.x;
+              ax.tx = ta * ax.x; ay.tx = ta * ay.x; az.tx = ta * az.x;
+              ax.tx2 = ax.tx * ax.tx; ay.tx2 = ay.tx * ay.tx; az.tx2 = az.tx * az.tx;
+              if (big) shell_prim_chi<ND, true>(ax, ay, az, l.x, l.y, l.z, ta, ex, p.chi_mode, chi);   // :2755-2768
+              else shell_prim_chi<ND, false>(ax, ay, az, l.x, l.y, l.z, ta, ex, p.chi_mode, chi);
               nz = true;
             }
           }

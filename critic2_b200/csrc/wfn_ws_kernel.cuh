@@ -156,77 +156,6 @@ __device__ __forceinline__ void ws_prod_bbox(double lo[3], double hi[3], const W
 // k = 0, 2 and k = 1, 3 from different bank halves: two conflict-free wavefronts, the minimum for 256 bytes.
 __device__ __forceinline__ int ws_a_index(int k, int pt) { return k * 16 + (pt ^ ((k & 1) << 3)); }
 
-// ---- chi of the primitives of ONE SHELL at one point (generator warps) ------------------------------------------------
-// The generators share the FP64 unit with the consumers' DMMAs and lose almost every arbitration (measured: ~170 cycles per
-// FP64 instruction while two consumer warps stream DMMAs), so what counts here is the NUMBER of FP64 instructions a warp
-// issues: everything common to the primitives of a shell -- displacement, squares, screen, exp, 2a, 2a x, (2a x)^2 -- is
-// computed once per (point, shell), and what depends on (lx, ly, lz) is picked with selects (integer pipe), which also keeps
-// the two half-warps (two shells) on one instruction stream.  Same formulas as axis_terms / prim_chi (wfn_device.cuh;
-// src/wfn_private@proc.F90:2755-2768): f0 = x^l, f1 = l x^(l-1) - 2a x^(l+1), f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + (2a x)^2 x^l.
-struct WsShellAxis {
-  double x, x2, twox, tx, tx2;   // displacement, its square, 2x, 2a x, (2a x)^2
-};
-__constant__ double c_ws_lf[8] = {0, 1, 2, 3, 4, 5, 6, 7};          // l
-__constant__ double c_ws_ll1[8] = {0, 0, 2, 6, 12, 20, 30, 42};     // l (l - 1)
-__constant__ double c_ws_2l1[8] = {1, 3, 5, 7, 9, 11, 13, 15};      // 2 l + 1
-
-// BIG = false: l <= 2 (s, p, d shells): no multiplication for the powers.  ta = 2a.
-template <int ND, bool BIG>
-__device__ __forceinline__ void ws_axis(const WsShellAxis &a, int l, double ta, double &f0, double &f1, double &f2) {
-  if (!BIG) {
-    f0 = l == 2 ? a.x2 : (l == 1 ? a.x : 1.0);
-    if (ND > 1) {
-      const double lpm1 = l == 2 ? a.twox : (l == 1 ? 1.0 : 0.0);   // l x^(l-1)
-      f1 = fma(-a.tx, f0, lpm1);
-      if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? 2.0 : 0.0);
-    }
-  } else {
-    const double x4 = a.x2 * a.x2;
-    const int n = l - 2;
-    const double pm2 = l >= 2 ? ((n & 1) ? a.x : 1.0) * ((n & 2) ? a.x2 : 1.0) * ((n & 4) ? x4 : 1.0) : 0.0;
-    const double pm1 = l >= 2 ? pm2 * a.x : (l == 1 ? 1.0 : 0.0);
-    f0 = l >= 1 ? pm1 * a.x : 1.0;
-    if (ND > 1) {
-      f1 = fma(-a.tx, f0, c_ws_lf[l & 7] * pm1);
-      if (ND > 4) f2 = fma(f0, fma(-c_ws_2l1[l & 7], ta, a.tx2), c_ws_ll1[l & 7] * pm2);
-    }
-  }
-}
-
-template <int ND, bool BIG>
-__device__ __forceinline__ void ws_shell_prim_chi(const WsShellAxis &ax, const WsShellAxis &ay, const WsShellAxis &az, int lx, int ly,
-                                                  int lz, double ta, double ex, int mode, double *chi) {
-  double x0, x1 = 0, x2 = 0, y0, y1 = 0, y2 = 0, z0, z1 = 0, z2 = 0;
-  if (ND == 1 && (mode & 3)) {   // value-only launches: the k-th Cartesian derivative as the "value" (WfnParams::chi_mode)
-    ws_axis<4, BIG>(ax, lx, ta, x0, x1, x2);
-    ws_axis<4, BIG>(ay, ly, ta, y0, y1, y2);
-    ws_axis<4, BIG>(az, lz, ta, z0, z1, z2);
-    const int k = mode & 3;
-    chi[0] = (k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1)) * ex;
-    return;
-  }
-  ws_axis<ND, BIG>(ax, lx, ta, x0, x1, x2);
-  ws_axis<ND, BIG>(ay, ly, ta, y0, y1, y2);
-  ws_axis<ND, BIG>(az, lz, ta, z0, z1, z2);
-  const double xe = x0 * ex, yz = y0 * z0;
-  chi[0] = xe * yz;
-  if (ND > 1) {
-    const double yze = yz * ex, xze = xe * z0, xye = xe * y0;
-    chi[ND > 1 ? 1 : 0] = x1 * yze;
-    chi[ND > 1 ? 2 : 0] = y1 * xze;
-    chi[ND > 1 ? 3 : 0] = z1 * xye;
-    if (ND > 4) {
-      const double ye = y0 * ex, ze = z0 * ex;
-      chi[ND > 4 ? 4 : 0] = x2 * yze;
-      chi[ND > 4 ? 5 : 0] = y2 * xze;
-      chi[ND > 4 ? 6 : 0] = z2 * xye;
-      chi[ND > 4 ? 7 : 0] = (x1 * y1) * ze;
-      chi[ND > 4 ? 8 : 0] = (x1 * z1) * ye;
-      chi[ND > 4 ? 9 : 0] = (z1 * y1) * xe;
-    }
-  }
-}
-
 template <class C>
 __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid) {
   constexpr int ND = C::ND, P = C::P, KC = C::KC, NGW = C::NPW - 1, NGT = 32 * NGW;
@@ -429,7 +358,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
         const long long bits = __double_as_longlong(r1.w);
         const int off = (int)(bits & 0xffffff), cnt = (int)((bits >> 24) & 0xff);
         const int cmax = max(cnt, __shfl_xor_sync(~0u, cnt, 16));
-        WsShellAxis ax, ay, az;
+        ShellAxis ax, ay, az;
         ax.x = px - xa.x; ay.x = py - xa.y; az.x = pz - xa.z;
         ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x; az.x2 = az.x * az.x;
         const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), az.x2);
@@ -461,9 +390,9 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
 #pragma unroll
             for (int d = 0; d < ND; d++) chi[d] = 0.0;
           } else if (__any_sync(~0u, (lx | ly | lz) > 2))
-            ws_shell_prim_chi<ND, true>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+            shell_prim_chi<ND, true>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
           else
-            ws_shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+            shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
           const int pos = off + i;
           if (on && (!(C2_WS_DIAG & 32) || chi[0] == 1.2345)) {
             double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
