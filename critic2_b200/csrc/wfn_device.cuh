@@ -84,76 +84,165 @@ __device__ __forceinline__ void prim_chi(double x, double y, double z, int lx, i
   }
 }
 
+// exp(t) for t <= 0 with 12 FP64 instructions and a dependency chain of ~9 (CUDA's exp: ~21 in one chain): the generator
+// warps pay for every FP64 instruction many times over (see below).  t = k ln2/32 + r, |r| <= ln2/64; exp(t) = 2^(k>>5)
+// T[k&31] (1 + r q(r)) with the degree-6 Taylor polynomial (remainder 3.5e-18) and T = 2^(j/32) as hi + lo.  Maximum error
+// 0.56 ulp against a long-double reference over 2e7 arguments in [-700, 0] (CPU emulation with fma()); below -700 (never
+// inside a primitive's cutoff radius) the library function takes over.
+static __device__ const double2 g_exp_tab[32] = {
+    {1.0, 0.0}, {1.0218971486541166, 5.109225028973444e-17},
+    {1.0442737824274138, 8.551889705537965e-17}, {1.0671404006768237, -7.899853966841582e-17},
+    {1.0905077326652577, -3.046782079812471e-17}, {1.1143867425958924, 1.0410278456845571e-16},
+    {1.1387886347566916, 8.912812676025408e-17}, {1.1637248587775775, 3.8292048369240935e-17},
+    {1.189207115002721, 3.982015231465646e-17}, {1.215247359980469, -7.712630692681488e-17},
+    {1.241857812073484, 4.658027591836937e-17}, {1.2690509571917332, 2.667932131342186e-18},
+    {1.2968395546510096, 2.5382502794888315e-17}, {1.3252366431597413, -2.8587312100388614e-17},
+    {1.3542555469368927, 7.70094837980299e-17}, {1.383909881963832, -6.770511658794786e-17},
+    {1.4142135623730951, -9.667293313452913e-17}, {1.4451808069770467, -3.0237581349939873e-17},
+    {1.4768261459394993, -3.483994556892796e-17}, {1.5091644275934228, -1.016455327754295e-16},
+    {1.5422108254079407, 7.949834809697621e-17}, {1.5759808451078865, -1.0136916471278304e-17},
+    {1.6104903319492543, 2.4707192569797888e-17}, {1.645755478153965, -1.0125679913674773e-16},
+    {1.681792830507429, 8.199010020581497e-17}, {1.718619298122478, -1.851380418263111e-17},
+    {1.7562521603732995, 2.960140695448873e-17}, {1.7947090750031072, 1.8227458427912087e-17},
+    {1.8340080864093424, 3.283107224245627e-17}, {1.8741676341103, -6.122763413004143e-17},
+    {1.9152065613971474, -1.0619946056195963e-16}, {1.9571441241754002, 8.960767791036668e-17},
+};
+__device__ __forceinline__ double exp_neg(double t) {
+  if (t < -700.0) return exp(t);
+  const double M = 6755399441055744.0;                       // 1.5 * 2^52: the low word of t*32/ln2 + M is round(t*32/ln2)
+  const double kf = fma(t, 46.16624130844683, M);
+  const int k = __double2loint(kf);
+  const double kd = kf - M;
+  double r = fma(kd, -0.02166084938653512, t);               // ln2/32: 32 significant bits, exact product
+  r = fma(kd, -5.9631716539705866e-12, r);
+  double q = fma(r, 1.0 / 720, 1.0 / 120);
+  q = fma(q, r, 1.0 / 24);
+  q = fma(q, r, 1.0 / 6);
+  q = fma(q, r, 0.5);
+  q = fma(q, r, 1.0);
+  q = q * r;                                                 // exp(r) - 1
+  const double2 tb = __ldg(&g_exp_tab[k & 31]);
+  const double v = fma(tb.x, q, tb.y) + tb.x;
+  return __hiloint2double(__double2hiint(v) + ((k >> 5) << 20), __double2loint(v));
+}
+
 // ---- chi of the primitives of ONE SHELL at one point -----------------------------------------------------------------
 // The generator warps of wfn_ws_kernel.cuh share the FP64 unit with the consumers' DMMAs and lose almost every
 // arbitration (tools/fp64_share.cu: 2500-9700 cycles per DFMA next to two DMMA-streaming warps), and the warp-autonomous
 // kernel's FP64 ALU work shares the unit with its own DMMAs: what counts is the NUMBER of FP64 instructions a warp issues.
-// Everything common to the primitives of a shell -- displacement, squares, 2a, 2a x, (2a x)^2 (and, in the generators,
-// screen and exp) -- is computed once per (point, shell); what depends on (lx, ly, lz) is picked with selects (integer
-// pipe), which also keeps lanes with different angular momenta on one instruction stream.  Same formulas as axis_terms /
+// Everything common to the primitives of a shell -- displacement, squares, 2a, 2a x, (2a x)^2, screen and exp -- is
+// computed once per (point, shell); what depends on (lx, ly, lz) is picked with selects (integer pipe), which also keeps
+// lanes with different angular momenta on one instruction stream; the z axis carries the exponential (its base values are
+// multiplied by e = exp(-a r^2) once per shell), so no product of a primitive needs it.  Same formulas as axis_terms /
 // prim_chi above (src/wfn_private@proc.F90:2755-2768): f0 = x^l, f1 = l x^(l-1) - 2a x^(l+1),
-// f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + (2a x)^2 x^l; 29 FP64 instructions per primitive for l <= 2 (a branch-free prim_chi: 65).
+// f2 = l(l-1) x^(l-2) - 2a(2l+1) x^l + (2a x)^2 x^l; 25 FP64 instructions per primitive for l <= 2 (a branch-free
+// prim_chi: 65).
 struct ShellAxis {
   double x, x2, twox, tx, tx2;   // displacement, its square, 2x, 2a x, (2a x)^2
 };
+struct ShellAxisE {              // the axis that carries e = exp(-a r^2)
+  double one, x, x2, twox, two;  // e, e x, e x^2, 2 e x, 2 e
+  double tx, tx2, xr;            // 2a x, (2a x)^2, x (unscaled)
+};
+__device__ __forceinline__ void shell_axis_setup(ShellAxis &a, double ta) {   // a.x, a.x2 set by the caller
+  a.twox = a.x + a.x;
+  a.tx = ta * a.x;
+  a.tx2 = a.tx * a.tx;
+}
+__device__ __forceinline__ void shell_axis_setup(ShellAxisE &a, double x, double x2, double ta, double e) {
+  a.xr = x;
+  a.tx = ta * x;
+  a.tx2 = a.tx * a.tx;
+  a.one = e;
+  a.x = e * x;
+  a.x2 = e * x2;
+  a.twox = a.x + a.x;
+  a.two = e + e;
+}
 static __constant__ double c_sh_lf[8] = {0, 1, 2, 3, 4, 5, 6, 7};          // l
 static __constant__ double c_sh_ll1[8] = {0, 0, 2, 6, 12, 20, 30, 42};     // l (l - 1)
 static __constant__ double c_sh_2l1[8] = {1, 3, 5, 7, 9, 11, 13, 15};      // 2 l + 1
 
-// BIG = false: l <= 2 (s, p, d shells): no multiplication for the powers.  ta = 2a.
-template <int ND, bool BIG>
+// l <= 2 (s, p, d shells): no multiplication for the powers.  ta = 2a.
+template <int ND>
 __device__ __forceinline__ void shell_axis(const ShellAxis &a, int l, double ta, double &f0, double &f1, double &f2) {
-  if (!BIG) {
-    f0 = l == 2 ? a.x2 : (l == 1 ? a.x : 1.0);
-    if (ND > 1) {
-      const double lpm1 = l == 2 ? a.twox : (l == 1 ? 1.0 : 0.0);   // l x^(l-1)
-      f1 = fma(-a.tx, f0, lpm1);
-      if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? 2.0 : 0.0);
-    }
-  } else {
-    const double x4 = a.x2 * a.x2;
-    const int n = l - 2;
-    const double pm2 = l >= 2 ? ((n & 1) ? a.x : 1.0) * ((n & 2) ? a.x2 : 1.0) * ((n & 4) ? x4 : 1.0) : 0.0;
-    const double pm1 = l >= 2 ? pm2 * a.x : (l == 1 ? 1.0 : 0.0);
-    f0 = l >= 1 ? pm1 * a.x : 1.0;
-    if (ND > 1) {
-      f1 = fma(-a.tx, f0, c_sh_lf[l & 7] * pm1);
-      if (ND > 4) f2 = fma(f0, fma(-c_sh_2l1[l & 7], ta, a.tx2), c_sh_ll1[l & 7] * pm2);
-    }
+  f0 = l == 2 ? a.x2 : (l == 1 ? a.x : 1.0);
+  if (ND > 1) {
+    const double lpm1 = l == 2 ? a.twox : (l == 1 ? 1.0 : 0.0);   // l x^(l-1)
+    f1 = fma(-a.tx, f0, lpm1);
+    if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? 2.0 : 0.0);
   }
 }
+template <int ND>
+__device__ __forceinline__ void shell_axis(const ShellAxisE &a, int l, double ta, double &f0, double &f1, double &f2) {
+  f0 = l == 2 ? a.x2 : (l == 1 ? a.x : a.one);
+  if (ND > 1) {
+    const double lpm1 = l == 2 ? a.twox : (l == 1 ? a.one : 0.0);
+    f1 = fma(-a.tx, f0, lpm1);
+    if (ND > 4) f2 = fma(f0, fma(l == 2 ? -5.0 : (l == 1 ? -3.0 : -1.0), ta, a.tx2), l == 2 ? a.two : 0.0);
+  }
+}
+// any l up to 7 (f shells and up): powers by multiplication, e applied at the end
+template <int ND>
+__device__ __forceinline__ void shell_axis_big(double x, double x2, double tx, double tx2, int l, double ta, double e, double &f0,
+                                               double &f1, double &f2) {
+  const double x4 = x2 * x2;
+  const int n = l - 2;
+  const double pm2 = l >= 2 ? ((n & 1) ? x : 1.0) * ((n & 2) ? x2 : 1.0) * ((n & 4) ? x4 : 1.0) : 0.0;
+  const double pm1 = l >= 2 ? pm2 * x : (l == 1 ? 1.0 : 0.0);
+  f0 = l >= 1 ? pm1 * x : 1.0;
+  if (ND > 1) {
+    f1 = fma(-tx, f0, c_sh_lf[l & 7] * pm1) * e;
+    if (ND > 4) f2 = fma(f0, fma(-c_sh_2l1[l & 7], ta, tx2), c_sh_ll1[l & 7] * pm2) * e;
+  }
+  f0 *= e;
+}
 
+// chi(1:ND) of one primitive of the shell; mode = WfnParams::chi_mode (value-only launches: bits 0-1 select the k-th
+// Cartesian derivative as the "value")
 template <int ND, bool BIG>
-__device__ __forceinline__ void shell_prim_chi(const ShellAxis &ax, const ShellAxis &ay, const ShellAxis &az, int lx, int ly,
-                                                  int lz, double ta, double ex, int mode, double *chi) {
+__device__ __forceinline__ void shell_prim_chi(const ShellAxis &ax, const ShellAxis &ay, const ShellAxisE &az, int lx, int ly,
+                                               int lz, double ta, int mode, double *chi) {
   double x0, x1 = 0, x2 = 0, y0, y1 = 0, y2 = 0, z0, z1 = 0, z2 = 0;
-  if (ND == 1 && (mode & 3)) {   // value-only launches: the k-th Cartesian derivative as the "value" (WfnParams::chi_mode)
-    shell_axis<4, BIG>(ax, lx, ta, x0, x1, x2);
-    shell_axis<4, BIG>(ay, ly, ta, y0, y1, y2);
-    shell_axis<4, BIG>(az, lz, ta, z0, z1, z2);
+  if (ND == 1 && (mode & 3)) {
+    if (BIG) {
+      shell_axis_big<4>(ax.x, ax.x2, ax.tx, ax.tx2, lx, ta, 1.0, x0, x1, x2);
+      shell_axis_big<4>(ay.x, ay.x2, ay.tx, ay.tx2, ly, ta, 1.0, y0, y1, y2);
+      shell_axis_big<4>(az.xr, az.xr * az.xr, az.tx, az.tx2, lz, ta, az.one, z0, z1, z2);
+    } else {
+      shell_axis<4>(ax, lx, ta, x0, x1, x2);
+      shell_axis<4>(ay, ly, ta, y0, y1, y2);
+      shell_axis<4>(az, lz, ta, z0, z1, z2);
+    }
     const int k = mode & 3;
-    chi[0] = (k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1)) * ex;
+    chi[0] = k == 1 ? x1 * y0 * z0 : (k == 2 ? x0 * y1 * z0 : x0 * y0 * z1);
     return;
   }
-  shell_axis<ND, BIG>(ax, lx, ta, x0, x1, x2);
-  shell_axis<ND, BIG>(ay, ly, ta, y0, y1, y2);
-  shell_axis<ND, BIG>(az, lz, ta, z0, z1, z2);
-  const double xe = x0 * ex, yz = y0 * z0;
-  chi[0] = xe * yz;
-  if (ND > 1) {
-    const double yze = yz * ex, xze = xe * z0, xye = xe * y0;
-    chi[ND > 1 ? 1 : 0] = x1 * yze;
-    chi[ND > 1 ? 2 : 0] = y1 * xze;
-    chi[ND > 1 ? 3 : 0] = z1 * xye;
-    if (ND > 4) {
-      const double ye = y0 * ex, ze = z0 * ex;
-      chi[ND > 4 ? 4 : 0] = x2 * yze;
-      chi[ND > 4 ? 5 : 0] = y2 * xze;
-      chi[ND > 4 ? 6 : 0] = z2 * xye;
-      chi[ND > 4 ? 7 : 0] = (x1 * y1) * ze;
-      chi[ND > 4 ? 8 : 0] = (x1 * z1) * ye;
-      chi[ND > 4 ? 9 : 0] = (z1 * y1) * xe;
-    }
+  if (BIG) {
+    shell_axis_big<ND>(ax.x, ax.x2, ax.tx, ax.tx2, lx, ta, 1.0, x0, x1, x2);
+    shell_axis_big<ND>(ay.x, ay.x2, ay.tx, ay.tx2, ly, ta, 1.0, y0, y1, y2);
+    shell_axis_big<ND>(az.xr, az.xr * az.xr, az.tx, az.tx2, lz, ta, az.one, z0, z1, z2);
+  } else {
+    shell_axis<ND>(ax, lx, ta, x0, x1, x2);
+    shell_axis<ND>(ay, ly, ta, y0, y1, y2);
+    shell_axis<ND>(az, lz, ta, z0, z1, z2);
+  }
+  if (ND == 1) {
+    chi[0] = x0 * y0 * z0;
+    return;
+  }
+  const double yz = y0 * z0, xz = x0 * z0, xy = x0 * y0;
+  chi[0] = x0 * yz;
+  chi[ND > 1 ? 1 : 0] = x1 * yz;
+  chi[ND > 1 ? 2 : 0] = y1 * xz;
+  chi[ND > 1 ? 3 : 0] = xy * z1;
+  if (ND > 4) {
+    chi[ND > 4 ? 4 : 0] = x2 * yz;
+    chi[ND > 4 ? 5 : 0] = y2 * xz;
+    chi[ND > 4 ? 6 : 0] = xy * z2;
+    chi[ND > 4 ? 7 : 0] = (x1 * y1) * z0;
+    chi[ND > 4 ? 8 : 0] = x1 * (y0 * z1);
+    chi[ND > 4 ? 9 : 0] = x0 * (y1 * z1);
   }
 }
 

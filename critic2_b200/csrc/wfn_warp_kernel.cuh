@@ -194,17 +194,20 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_warp_kernel(const __grid_c
           if (real && valid) {
             const double4 xa = w.shell_xa[e.y];
             const double2 cut = w.shell_cut[e.y];
-            ShellAxis ax, ay, az;
-            ax.x = px - xa.x; ay.x = py - xa.y; az.x = pz - xa.z;
-            ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x; az.x2 = az.x * az.x;
-            const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), az.x2);
-            if (within_cut(ax.x, ay.x, az.x, d2, cut.x, cut.y)) {                 // :2747
-              const double ta = xa.w + xa.w, ex = exp(-xa.w * d2);                // :2749
-              ax.twox = ax.x + ax.x; ay.twox = ay.x + ay.x; az.twox = az.x + az.x;
-              ax.tx = ta * ax.x; ay.tx = ta * ay.x; az.tx = ta * az.x;
-              ax.tx2 = ax.tx * ax.tx; ay.tx2 = ay.tx * ay.tx; az.tx2 = az.tx * az.tx;
-              if (big) shell_prim_chi<ND, true>(ax, ay, az, l.x, l.y, l.z, ta, ex, p.chi_mode, chi);   // :2755-2768
-              else shell_prim_chi<ND, false>(ax, ay, az, l.x, l.y, l.z, ta, ex, p.chi_mode, chi);
+            ShellAxis ax, ay;
+            ax.x = px - xa.x; ay.x = py - xa.y;
+            const double zr = pz - xa.z;
+            ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x;
+            const double z2 = zr * zr;
+            const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), z2);
+            if (within_cut(ax.x, ay.x, zr, d2, cut.x, cut.y)) {                   // :2747
+              const double ta = xa.w + xa.w;
+              ShellAxisE az;
+              shell_axis_setup(ax, ta);
+              shell_axis_setup(ay, ta);
+              shell_axis_setup(az, zr, z2, ta, exp_neg(-xa.w * d2));              // :2749
+              if (big) shell_prim_chi<ND, true>(ax, ay, az, l.x, l.y, l.z, ta, p.chi_mode, chi);   // :2755-2768
+              else shell_prim_chi<ND, false>(ax, ay, az, l.x, l.y, l.z, ta, p.chi_mode, chi);
               nz = true;
             }
           }

@@ -19,7 +19,8 @@
 // shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: the consumers keep their MMA
 // operands in registers (no shared-memory operand loads inside the loop).  16: consumer warps accumulate clock64() spent
 // waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
-// do not store the chi tiles.  64: no exp in the generators.
+// do not store the chi tiles.  64: no exp in the generators.  128: the generators
+// skip the arithmetic of every fourth shell pair (what a fourth generator warp would buy).
 #ifndef C2_WS_DIAG
 #define C2_WS_DIAG 0
 #endif
@@ -358,12 +359,14 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
         const long long bits = __double_as_longlong(r1.w);
         const int off = (int)(bits & 0xffffff), cnt = (int)((bits >> 24) & 0xff);
         const int cmax = max(cnt, __shfl_xor_sync(~0u, cnt, 16));
-        ShellAxis ax, ay, az;
-        ax.x = px - xa.x; ay.x = py - xa.y; az.x = pz - xa.z;
-        ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x; az.x2 = az.x * az.x;
-        const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), az.x2);
+        ShellAxis ax, ay;
+        ax.x = px - xa.x; ay.x = py - xa.y;
+        const double zr = pz - xa.z;
+        ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x;
+        const double z2 = zr * zr;
+        const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), z2);
         bool pass = has && pvalid && !(d2 > r1.z);                          // screen (:2747): outside the rounding band ...
-        if (pass && !(d2 < r1.y)) pass = !(norm2_ref(ax.x, ay.x, az.x) > r1.x);   // ... inside it, the reference's own norm2
+        if (pass && !(d2 < r1.y)) pass = !(norm2_ref(ax.x, ay.x, zr) > r1.x);   // ... inside it, the reference's own norm2
         if (!__any_sync(~0u, pass)) {   // no point of the sub-tile within reach of either shell
           for (int i = 0; i < cnt; i++) {
             const int pos = off + i;
@@ -374,11 +377,12 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
           continue;
         }
         const double al = xa.w;
-        const double ex = pass ? ((C2_WS_DIAG & 64) ? 1.0 - al * d2 : exp(-al * d2)) : 0.0;   // :2749; 0 also zeroes every chi of the lane
+        const double ex = pass ? ((C2_WS_DIAG & 64) ? 1.0 - al * d2 : exp_neg(-al * d2)) : 0.0;   // :2749; 0 also zeroes every chi of the lane
         const double ta = al + al;
-        ax.twox = ax.x + ax.x; ay.twox = ay.x + ay.x; az.twox = az.x + az.x;
-        ax.tx = ta * ax.x; ay.tx = ta * ay.x; az.tx = ta * az.x;
-        ax.tx2 = ax.tx * ax.tx; ay.tx2 = ay.tx * ay.tx; az.tx2 = az.tx * az.tx;
+        ShellAxisE az;
+        shell_axis_setup(ax, ta);
+        shell_axis_setup(ay, ta);
+        shell_axis_setup(az, zr, z2, ta, ex);
         unsigned long long lw = (unsigned long long)__double_as_longlong(r2.x);
         for (int i = 0; i < cmax; i++) {
           const bool on = i < cnt;
@@ -386,13 +390,13 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
           lw >>= 10;
           if (i % 6 == 5) lw = (unsigned long long)__double_as_longlong(i < 6 ? r2.y : (i < 12 ? r2.z : r2.w));
           double chi[ND];
-          if (C2_WS_DIAG & 2) {
+          if ((C2_WS_DIAG & 2) || ((C2_WS_DIAG & 128) && ((j / NGW) & 3) == 3)) {
 #pragma unroll
             for (int d = 0; d < ND; d++) chi[d] = 0.0;
           } else if (__any_sync(~0u, (lx | ly | lz) > 2))
-            shell_prim_chi<ND, true>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+            shell_prim_chi<ND, true>(ax, ay, az, lx, ly, lz, ta, p.chi_mode, chi);
           else
-            shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, ex, p.chi_mode, chi);
+            shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, p.chi_mode, chi);
           const int pos = off + i;
           if (on && (!(C2_WS_DIAG & 32) || chi[0] == 1.2345)) {
             double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
