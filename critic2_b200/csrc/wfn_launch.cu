@@ -126,17 +126,17 @@ int wfn_choose_config(int nmo, int force) {
   if (nfrag <= 3) return 8 + nfrag;
   // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms; tools/probe_mid.py, profiles/r2_probe_mid.log):
   //   blocks          1      2      3      4      5
-  //   M2    (64)     57.9  112.4  166.8  221.5  275.9    54.5 per block + 3
-  //   L1    (112)   102.5  198.3  294.2                  96 per block + 6
-  //   WS    (112)   144.4  195.4  246.2                  93.6 + 50.9 per block (generators ahead, chi tiles re-used from L2)
-  //   WS64g (64)     68.7   98.8  142.0  185.6  229.4    generator-bound for one block, then 11 + 43.7 per block
-  // (before the shell-wise generators WS64g took 92.6 / 119.5 / 157.4 / 198.2 / 239.7 and WS 154 / 207 / 259.)  WS64g now wins
-  // from 65 to ~400 MOs (128 MOs: 98.8 against 112.4 ms = 69 % of the DMMA peak, 192: 71 %, 256: 72.5 %); 500-atom config 4
-  // (780 MOs): WS 89.6 % of the peak, L 62 %.
+  //   M2    (64)     58.0  112.4  167.1  221.4  276.0    54.5 per block + 3
+  //   L1    (112)   102.6  198.6  294.3                  96 per block + 6
+  //   WS    (112)   152.5  202.3  252.3                  102.5 + 49.9 per block (generators ahead, chi tiles re-used from L2)
+  //   WS64g (64)     68.1   96.5  138.2  180.5  221.6    generator-bound for one block, then 12 + 42 per block
+  // (before the shell-wise generators and the paired chi rows WS64g took 92.6 / 119.5 / 157.4 / 198.2 / 239.7.)  WS64g wins
+  // from 65 to ~400 MOs: 128 MOs 70.8 % of the DMMA peak, 192: 73.4 %, 256: 74.6 %, 300: 71.0 %; 500-atom config 4 (780 MOs):
+  // WS 89.8 % of the peak, L 62 %.
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
-  const double tM = 54.5 * bM + 3, tL = 96 * bL + 6, tW = 93.6 + 50.9 * bL;
-  const double tG = bM <= 1 ? 68.7 : (bM == 2 ? 98.8 : 11 + 43.7 * bM);
-  if (tG < tM && tG < tL && tG < tW) return 13;
+  const double tM = 54.5 * bM + 3, tL = 96 * bL + 6, tW = 102.5 + 49.9 * bL;
+  const double tG = bM <= 1 ? 68.1 : (bM == 2 ? 96.5 : 12 + 42.0 * bM);
+  if (bM <= 6 && tG < tM && tG < tL && tG < tW) return 13;   // measured up to five blocks; beyond 384 MOs the 112-column kernels
   if (tM <= tL && tM <= tW) return 8;
   return tL <= tW ? 4 : 6;
 }

@@ -16,8 +16,7 @@
 // Development diagnostics (tools/ws_diag.sh builds separate libraries with -DC2_WS_DIAG=bits; the shipped library has 0 and
 // none of this code).  Results of a diagnostic build are NOT valid field values: the bits remove work to see what the
 // tensor pipe is waiting for.  1: the streamer issues no TMA copies (stages complete at once; consumers multiply stale
-// shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: the consumers keep their MMA
-// operands in registers (no shared-memory operand loads inside the loop).  16: consumer warps accumulate clock64() spent
+// shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: (retired).  16: consumer warps accumulate clock64() spent
 // waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
 // do not store the chi tiles.  64: no exp in the generators.  128: the generators
 // skip the arithmetic of every fourth shell pair (what a fourth generator warp would buy).
@@ -50,6 +49,11 @@ struct WsCfg {
   static constexpr int ACHUNK = 32 * ND * P;    // chi-cache doubles per 32 primitives (the unit of WfnParams::acache_chunks)
   static_assert(KC % 4 == 0 && KC <= 64 && NKQ <= 32, "stage size");
   static constexpr int NI = NF0;                // most fragments per consumer warp
+  // chi tiles with derivative rows interleaved in pairs (one LDS.128 feeds two DMMA groups; see ws_a_index).  Only where
+  // the two consumer warps of a sub-partition carry the same number of fragments: with 4 + 3 the lighter warp gets through
+  // its stage even faster and the heavier one runs alone for longer (measured: 88.6 -> 87.4 % on the bench slab, while the
+  // 64-column variant gains 4 %)
+  static constexpr bool PAIRS = (ND_ % 2 == 0) && (NF0 == NF1);
   static constexpr int SB = NB + 4;             // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
   static constexpr int TSLOTS = 8;              // tile-info ring (>= NS + 3, see ws_generator)
@@ -150,12 +154,30 @@ __device__ __forceinline__ void ws_prod_bbox(double lo[3], double hi[3], const W
 // Hand-over: ready[b] (generator -> streamer, tile in buffer b complete) and freeb[b] (streamer -> generator, every
 // TMA load of the tile in buffer b has landed), both single-arrival mbarriers used with the usual phase parity.
 // ---------------------------------------------------------------------------------------------------------------
-// Layout of one (k-quad, derivative row) slice of a chi tile: 4 primitives x 16 points.  Primitive-major, so the 16 points a
-// generator half-warp evaluates for one primitive are one 128-byte line of the chi-tile cache (point-major slices made every
-// store instruction touch 32 sectors, 8 bytes each: the generators were bound by the store path); the two 8-point row groups
-// swap places for odd k, so the consumers' A-fragment load (lane = (row, k): 8 rows x 4 primitives of one row group) reads
-// k = 0, 2 and k = 1, 3 from different bank halves: two conflict-free wavefronts, the minimum for 256 bytes.
-__device__ __forceinline__ int ws_a_index(int k, int pt) { return k * 16 + (pt ^ ((k & 1) << 3)); }
+// Layout of the chi tile of one k-quad (4 primitives x 16 points x ND derivative rows).  Primitive-major slices, so the 16
+// points a generator half-warp evaluates for one primitive are contiguous in the chi-tile cache (point-major slices made
+// every store instruction touch 32 sectors, 8 bytes each: the generators were bound by the store path).  Derivative rows
+// can be interleaved in PAIRS (WsCfg::PAIRS): element (d, k, pt) sits at ((d / 2) * 64 + ws_a_index(k, pt)) * 2 + d % 2, so a
+// consumer lane fetches the operands of two derivative rows with one LDS.128 (half the operand loads of the MMA loop: a
+// warp that has the tensor pipe to itself issues DMMAs at 79-87 % of the peak with one shared-memory load per group of
+// 3-4, tools/dmma_issue.cu) and a generator lane stores them with one 16-byte store.  The point index is XOR-ed with 2k
+// (pairs) or 4k (plain 8-byte slices): a shared-memory wavefront serves 128 bytes, i.e. the 8 (16) consecutive
+// lanes = 2 (4) rows x 4 primitives of a consumer's A-fragment load, which this spreads over all 32 banks.
+template <bool PAIRS>
+__device__ __forceinline__ int ws_a_index(int k, int pt) { return k * 16 + (pt ^ ((PAIRS ? 2 : 4) * k)); }
+
+template <int ND, bool PAIRS>
+__device__ __forceinline__ void ws_store_chi(double *Aq, int k, int pt, const double *chi) {   // Aq: start of the k-quad's tile
+  const int ai = ws_a_index<PAIRS>(k, pt);
+  if (PAIRS) {
+#pragma unroll
+    for (int dp = 0; dp < ND / 2; dp++)
+      *reinterpret_cast<double2 *>(Aq + (dp * 64 + ai) * 2) = make_double2(chi[2 * dp], chi[(ND > 1) ? 2 * dp + 1 : 0]);
+  } else {
+#pragma unroll
+    for (int d = 0; d < ND; d++) Aq[d * 64 + ai] = chi[d];
+  }
+}
 
 template <class C>
 __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid) {
@@ -341,6 +363,9 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       // primitives together; slot k of the primitive list is column k % 4 of k-quad k / 4 (quads are contiguous in the
       // cache: chunk c starts at c * A_STAGE) ---------------------------------------------------------------------------
       const int hsh = lane & 16;
+      double zero[ND];
+#pragma unroll
+      for (int d = 0; d < ND; d++) zero[d] = 0.0;
       for (int j = warp; 2 * j < nact_sh; j += NGW) {
         const int si = 2 * j + (hsh >> 4);
         const bool has = si < nact_sh;
@@ -370,9 +395,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
         if (!__any_sync(~0u, pass)) {   // no point of the sub-tile within reach of either shell
           for (int i = 0; i < cnt; i++) {
             const int pos = off + i;
-            double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
-#pragma unroll
-            for (int d = 0; d < ND; d++) Aq[d * P * 4] = 0.0;
+            ws_store_chi<ND, C::PAIRS>(agbase + (size_t)(pos >> 2) * ND * P * 4, pos & 3, pt, zero);
           }
           continue;
         }
@@ -399,9 +422,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
             shell_prim_chi<ND, false>(ax, ay, az, lx, ly, lz, ta, p.chi_mode, chi);
           const int pos = off + i;
           if (on && (!(C2_WS_DIAG & 32) || chi[0] == 1.2345)) {
-            double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
-#pragma unroll
-            for (int d = 0; d < ND; d++) Aq[d * P * 4] = chi[d];
+            ws_store_chi<ND, C::PAIRS>(agbase + (size_t)(pos >> 2) * ND * P * 4, pos & 3, pt, chi);
           }
           const unsigned bal = __ballot_sync(~0u, on && pass);
           const unsigned hm = (bal >> hsh) & 0xffffu;
@@ -411,9 +432,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       // unused columns of the last k-quad: zeros (their C rows are whatever the stage held before)
       if (warp == 0)
         for (int pos = kact + (hsh >> 4); pos < ((kact + 3) & ~3); pos += 2) {
-          double *Aq = agbase + (size_t)(pos >> 2) * ND * P * 4 + ws_a_index(pos & 3, pt);
-#pragma unroll
-          for (int d = 0; d < ND; d++) Aq[d * P * 4] = 0.0;
+          ws_store_chi<ND, C::PAIRS>(agbase + (size_t)(pos >> 2) * ND * P * 4, pos & 3, pt, zero);
         }
 #if C2_WS_DIAG & 16
       gg_chi += clock64() - gg_t0;
@@ -552,29 +571,56 @@ __device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const 
 #pragma unroll
   for (int ni = 0; ni < NF; ni++) b[ni] = Bst[kq * 4 * SB + ni * 8];
   const double *Ak = Ast + (size_t)kq * ND * P * 4;
-  double a = Ak[0];
   bool more;
+  if (C::PAIRS) {                                        // Ast points at this lane's pair of derivative rows 0, 1
+    double2 a = *reinterpret_cast<const double2 *>(Ak);
 #pragma unroll 1
-  do {
-    more = kqm != 0;
-    const int kqn = more ? __ffs(kqm) - 1 : kq;
-    kqm &= kqm - 1;
-    double bn[NF];
+    do {
+      more = kqm != 0;
+      const int kqn = more ? __ffs(kqm) - 1 : kq;
+      kqm &= kqm - 1;
+      double bn[NF];
 #pragma unroll
-    for (int ni = 0; ni < NF; ni++) bn[ni] = (C2_WS_DIAG & 4) ? b[ni] : Bst[kqn * 4 * SB + ni * 8];
-    const double *An = Ast + (size_t)kqn * ND * P * 4;
+      for (int ni = 0; ni < NF; ni++) bn[ni] = Bst[kqn * 4 * SB + ni * 8];
+      const double *An = Ast + (size_t)kqn * ND * P * 4;
 #pragma unroll
-    for (int d = 0; d < ND; d++) {
-      const double an = (C2_WS_DIAG & 4) ? a : (d + 1 < ND) ? Ak[(d + 1) * P * 4] : An[0];
+      for (int dp = 0; dp < ND / 2; dp++) {
+        const double2 an = *reinterpret_cast<const double2 *>((dp + 1 < ND / 2) ? Ak + (dp + 1) * 128 : An);
 #pragma unroll
-      for (int ni = 0; ni < NF; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
-      a = an;
-    }
+        for (int ni = 0; ni < NF; ni++) dmma884(acc[2 * dp][ni][0], acc[2 * dp][ni][1], a.x, b[ni]);
 #pragma unroll
-    for (int ni = 0; ni < NF; ni++) b[ni] = bn[ni];
-    Ak = An;
-    kq = kqn;
-  } while (more);
+        for (int ni = 0; ni < NF; ni++) dmma884(acc[(ND > 1) ? 2 * dp + 1 : 0][ni][0], acc[(ND > 1) ? 2 * dp + 1 : 0][ni][1], a.y, b[ni]);
+        a = an;
+      }
+#pragma unroll
+      for (int ni = 0; ni < NF; ni++) b[ni] = bn[ni];
+      Ak = An;
+      kq = kqn;
+    } while (more);
+  } else {
+    double a = Ak[0];
+#pragma unroll 1
+    do {
+      more = kqm != 0;
+      const int kqn = more ? __ffs(kqm) - 1 : kq;
+      kqm &= kqm - 1;
+      double bn[NF];
+#pragma unroll
+      for (int ni = 0; ni < NF; ni++) bn[ni] = Bst[kqn * 4 * SB + ni * 8];
+      const double *An = Ast + (size_t)kqn * ND * P * 4;
+#pragma unroll
+      for (int d = 0; d < ND; d++) {
+        const double an = (d + 1 < ND) ? Ak[(d + 1) * P * 4] : An[0];
+#pragma unroll
+        for (int ni = 0; ni < NF; ni++) dmma884(acc[d][ni][0], acc[d][ni][1], a, b[ni]);
+        a = an;
+      }
+#pragma unroll
+      for (int ni = 0; ni < NF; ni++) b[ni] = bn[ni];
+      Ak = An;
+      kq = kqn;
+    } while (more);
+  }
 }
 
 template <class C, int NF>
@@ -584,7 +630,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
   const int wm = cw & 1, wn = cw >> 1;                 // row group (8 points) and warp column (0..3)
   const int f0 = wn < 2 ? wn * C::NF0 : 2 * C::NF0 + (wn - 2) * C::NF1;   // first fragment of this warp (4,4,3,3 for NB = 112)
   const int row = lane >> 2;
-  const int aoff = ws_a_index(lane & 3, wm * 8 + row);
+  const int aoff = ws_a_index<C::PAIRS>(lane & 3, wm * 8 + row) * (C::PAIRS ? 2 : 1);
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
   double acc[ND][NF][2];
