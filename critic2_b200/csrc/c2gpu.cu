@@ -23,9 +23,6 @@ int g_force_cfg = -1;
 int g_fmt_force_exact = 0;
 int g_super = 8;
 int g_nci_two_pass = 1;
-int g_empty_fast = 0;   // block-synchronous kernels: fast path for super-tiles without active shells.  Parity-green when on
-                        // (54 GPU tests), but no gain on BASELINE configs 1 and 2 (1.480 / 17.25 ms either way: the diffuse
-                        // aug- functions reach every super-tile of those grids), so it stays off
 
 int fail(int code, const std::string &msg) {
   g_err = msg;
@@ -171,7 +168,6 @@ int c2gpu_set_option(const char *name, int value) {
   if (!name) return 1;
   if (!strcmp(name, "wfn_cfg")) { g_force_cfg = value; return 0; }
   if (!strcmp(name, "super")) { if (value < 4 || value % 4) return 1; g_super = value; return 0; }
-  if (!strcmp(name, "empty_fast")) { g_empty_fast = value; return 0; }
   if (!strcmp(name, "nci_two_pass")) { g_nci_two_pass = value; return 0; }   // development: A/B of the NCIPLOT epilogue
   if (!strcmp(name, "fmt_force_exact")) { g_fmt_force_exact = value; return 0; }   // tests: big-integer rounding path
   return 1;

@@ -42,7 +42,6 @@ struct WfnParams {
   // (rho2, src/wfn_private@proc.F90:2104-2106,2209).  bit 2 (block-synchronous kernels): the MO sum is linear, sum_mo
   // occ phi -- with a one-MO handle that is the MO value of calculate_mo (:2447-2553).
   int chi_mode;
-  int empty_fast;       // 1: super-tiles no shell reaches skip the sub-tile machinery (block-synchronous kernels)
 };
 
 // NFRAG = 8-column MMA fragments per MO block, dealt to the WN warp columns: warp column wn owns
@@ -196,27 +195,6 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
     }
     __syncthreads();
     const int nnuc = s_int[3];
-
-    // ---- empty super-tile (no shell reaches its box: the vacuum border of a molecular cell): every point gets the tail of
-    // grd on zero sums (all outputs 0, or the core alone) without the sub-tile machinery (bounding boxes, S2, barriers)
-    if (ns == 0 && p.empty_fast) {
-      for (int q = tid; q < npsuper; q += NT) {
-        const int a = sa0 + q % g.sa, b = sb0 + (q / g.sa) % g.sb, c = sc0 + q / (g.sa * g.sb);
-        if (a >= na || b >= nb || c >= g.c1) continue;
-        bool isnuc = false;
-        if (nnuc > 0) {
-          double x[3], wc[3], wcr[3];
-          grid_point(g, a, b, c, x);
-          grd_wrap(p.xf, x, g.periodic, wc, wcr);
-          for (int i = 0; i < w.natom && !isnuc; i++) {
-            const double ddx = w.atom_xyz[3 * i] - wcr[0], ddy = w.atom_xyz[3 * i + 1] - wcr[1], ddz = w.atom_xyz[3 * i + 2] - wcr[2];
-            isnuc = (ddx * ddx + ddy * ddy + ddz * ddz) < 1e-10;      // src/environmod@proc.f90:677
-          }
-        }
-        emit_point_call(p.o, out_index(g, a, b, c), 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, isnuc, p.nci_const);
-      }
-      continue;
-    }
 
     for (int sub = 0; sub < nsub_a * nsub_b * nsub_c; sub++) {
       const int ta0 = sa0 + (sub % nsub_a) * g.ta, tb0 = sb0 + ((sub / nsub_a) % nsub_b) * g.tb;
