@@ -19,7 +19,8 @@
 // shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: (retired).  16: consumer warps accumulate clock64() spent
 // waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
 // do not store the chi tiles.  64: no exp in the generators.  128: the generators
-// skip the arithmetic of every fourth shell pair (what a fourth generator warp would buy).
+// skip the arithmetic of every fourth shell pair (what a fourth generator warp would buy).  256: the consumers issue no
+// DMMAs (the kernel time is then what the producers need when they have the FP64 unit to themselves).
 #ifndef C2_WS_DIAG
 #define C2_WS_DIAG 0
 #endif
@@ -669,7 +670,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     if (!(flags & 8)) {
       const double *Ast = S.As + stg * C::A_STAGE + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
-      ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+      if (!(C2_WS_DIAG & 256)) ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
 #if C2_WS_DIAG & 16
       dg_mma += clock64() - dg1;
       dg_cnt += (unsigned long long)__popc((unsigned)h.kqmask[wm]) * ND * NF;
