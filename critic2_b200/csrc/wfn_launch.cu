@@ -126,16 +126,15 @@ int wfn_choose_config(int nmo, int force) {
   if (nfrag <= 3) return 8 + nfrag;
   // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms; tools/probe_mid.py, profiles/r2_probe_mid.log):
   //   blocks          1      2      3      4      5
-  //   M2    (64)     58.0  112.4  167.1  221.4  276.0    54.5 per block + 3
+  //   M2    (64)     57.2  110.5  163.7  216.9  269.9    53.5 per block + 3.5
   //   L1    (112)   102.6  198.6  294.3                  96 per block + 6
-  //   WS    (112)   152.5  202.3  252.3                  102.5 + 49.9 per block (generators ahead, chi tiles re-used from L2)
-  //   WS64g (64)     68.1   96.5  138.2  180.5  221.6    generator-bound for one block, then 12 + 42 per block
-  // (before the shell-wise generators and the paired chi rows WS64g took 92.6 / 119.5 / 157.4 / 198.2 / 239.7.)  WS64g wins
-  // from 65 to ~400 MOs: 128 MOs 70.8 % of the DMMA peak, 192: 73.4 %, 256: 74.6 %, 300: 71.0 %; 500-atom config 4 (780 MOs):
-  // WS 89.8 % of the peak, L 62 %.
+  //   WS    (112)   152.3  202.3  252.6                  102.3 + 50.1 per block (generators ahead, chi tiles re-used from L2)
+  //   WS64g (64)     70.1   96.5  129.1  168.9  208.9    generator-bound for one block, then 9 + 40 per block
+  // (first version of WS64g: 92.6 / 119.5 / 157.4 / 198.2 / 239.7.)  WS64g wins from 65 to 384 MOs: 128 MOs 70.8 % of the
+  // DMMA peak, 192: 78.6 %, 256: 79.7 %, 300: 75.4 %; 500-atom config 4 (780 MOs): WS 89.8 % of the peak, L 62 %.
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
-  const double tM = 54.5 * bM + 3, tL = 96 * bL + 6, tW = 102.5 + 49.9 * bL;
-  const double tG = bM <= 1 ? 68.1 : (bM == 2 ? 96.5 : 12 + 42.0 * bM);
+  const double tM = 53.5 * bM + 3.5, tL = 96 * bL + 6, tW = 102.3 + 50.1 * bL;
+  const double tG = bM <= 1 ? 70.1 : (bM == 2 ? 96.5 : 9 + 40.0 * bM);
   if (bM <= 6 && tG < tM && tG < tL && tG < tW) return 13;   // measured up to five blocks; beyond 384 MOs the 112-column kernels
   if (tM <= tL && tM <= tW) return 8;
   return tL <= tW ? 4 : 6;

@@ -12,6 +12,7 @@
 //     (sub-tile, MO block, chunk) steps is continuous, so producers run ahead across block and tile boundaries.
 #pragma once
 #include "wfn_kernel.cuh"
+#include <type_traits>
 
 // Development diagnostics (tools/ws_diag.sh builds separate libraries with -DC2_WS_DIAG=bits; the shipped library has 0 and
 // none of this code).  Results of a diagnostic build are NOT valid field values: the bits remove work to see what the
@@ -562,8 +563,11 @@ __device__ void ws_streamer(const WfnParams &p, const WsShared<C> &S, int lane) 
 // Operands of the next k-quad / derivative row are fetched from shared memory while the current DMMAs issue, so the
 // tensor pipe does not drain between k-quads (the first version reloaded everything at the top of each k-quad and
 // spilled accumulators: ~8 % of the in-loop time was both warps of a sub-partition waiting on operands).
+// MMAs of one stage, first form: operands of the next k-quad / derivative row fetched while the current DMMAs issue, in
+// the order ptxas picks.  Kept for the 4 + 3 fragment split, where it measures 1 % better than ws_mma_stage below (whatever
+// makes the consumers of that configuration stream more densely takes slack from the generators).
 template <class C, int NF>
-__device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const double *Ast, const double *Bst, unsigned kqm) {
+__device__ __forceinline__ void ws_mma_stage_v1(double (&acc)[C::ND][NF][2], const double *Ast, const double *Bst, unsigned kqm) {
   constexpr int ND = C::ND, P = C::P, SB = C::SB;
   if (kqm == 0) return;                                  // all 8 points x 32 primitives masked (warp-uniform)
   int kq = __ffs(kqm) - 1;
@@ -624,6 +628,93 @@ __device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const 
   }
 }
 
+// Shared-memory operand loads as volatile asm, so they keep their place between the (volatile asm) DMMAs.
+__device__ __forceinline__ void ws_lds(double &v, uint32_t addr) { asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr)); }
+__device__ __forceinline__ void ws_lds(double2 &v, uint32_t addr) {
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+}
+
+// The DMMAs of one k-quad: derivative rows (or pairs of rows) in turn, NF fragments each; a_cur holds the operand of the
+// first step on entry and the operand of the NEXT k-quad's first step on exit.  WHERE the loads sit matters (ncu, source
+// page): a DMMA reads its source registers when it executes, up to four queue slots after it was issued, so a load that
+// re-uses an operand register right after the group that read it waits for that group to drain (9.7 % of the 4-fragment
+// warps' samples were this short-scoreboard wait).  Each step therefore issues its leading DMMA first -- that one waits for
+// a queue slot, by which time the previous group has executed -- and only then the load of the next step's operand into
+// the register the previous group used; the B operands of the next k-quad are loaded into the set the PREVIOUS k-quad
+// used (two sets ping-pong, the caller alternates them: no register moves) during step 1.
+template <class C, int NF, class AT>
+__device__ __forceinline__ void ws_mma_kquad(double (&acc)[C::ND][NF][2], AT &a_cur, AT &a_oth, const double (&b)[NF], double (&bn)[NF],
+                                             uint32_t ak, uint32_t an_first, uint32_t bn_addr) {
+  constexpr int ND = C::ND, SB = C::SB;
+  constexpr bool PAIRS = C::PAIRS;
+  constexpr int NSTEP = PAIRS ? ND / 2 : ND;
+  constexpr uint32_t STEP_BYTES = (PAIRS ? 128 : 64) * 8;   // one derivative row = 64 doubles, a pair = 128
+#pragma unroll
+  for (int st = 0; st < NSTEP; st++) {
+    AT &cur = (st & 1) ? a_oth : a_cur;
+    AT &nxt = (st & 1) ? a_cur : a_oth;
+    const int d0 = PAIRS ? 2 * st : st;
+    if (PAIRS) {
+      const double2 &c2 = reinterpret_cast<const double2 &>(cur);
+      dmma884(acc[d0][0][0], acc[d0][0][1], c2.x, b[0]);
+      ws_lds(nxt, st + 1 < NSTEP ? ak + (st + 1) * STEP_BYTES : an_first);
+#pragma unroll
+      for (int ni = 1; ni < NF; ni++) dmma884(acc[d0][ni][0], acc[d0][ni][1], c2.x, b[ni]);
+      if (st == 1) {
+#pragma unroll
+        for (int ni = 0; ni < NF; ni++) ws_lds(bn[ni], bn_addr + ni * 64);
+      }
+#pragma unroll
+      for (int ni = 0; ni < NF; ni++) dmma884(acc[(ND > 1) ? d0 + 1 : 0][ni][0], acc[(ND > 1) ? d0 + 1 : 0][ni][1], c2.y, b[ni]);
+    } else {
+      const double &c1 = reinterpret_cast<const double &>(cur);
+      dmma884(acc[d0][0][0], acc[d0][0][1], c1, b[0]);
+      ws_lds(nxt, st + 1 < NSTEP ? ak + (st + 1) * STEP_BYTES : an_first);
+#pragma unroll
+      for (int ni = 1; ni < NF; ni++) dmma884(acc[d0][ni][0], acc[d0][ni][1], c1, b[ni]);
+      if (st == (NSTEP > 1 ? 1 : 0)) {
+#pragma unroll
+        for (int ni = 0; ni < NF; ni++) ws_lds(bn[ni], bn_addr + ni * 64);
+      }
+    }
+  }
+}
+
+template <class C, int NF>
+__device__ __forceinline__ void ws_mma_stage(double (&acc)[C::ND][NF][2], const double *Ast, const double *Bst, unsigned kqm) {
+  constexpr int ND = C::ND, P = C::P, SB = C::SB;
+  constexpr int NSTEP = C::PAIRS ? ND / 2 : ND;
+  using AT = typename std::conditional<C::PAIRS, double2, double>::type;
+  if (kqm == 0) return;                                  // all 8 points x 32 primitives masked (warp-uniform)
+  const uint32_t a0 = smem_u32(Ast), b0a = smem_u32(Bst);
+  constexpr uint32_t KQ_A = ND * P * 4 * 8, KQ_B = 4 * SB * 8;   // bytes per k-quad of the chi tile / of the C rows
+  int kq = __ffs(kqm) - 1;
+  kqm &= kqm - 1;
+  double b0[NF], b1[NF];
+#pragma unroll
+  for (int ni = 0; ni < NF; ni++) ws_lds(b0[ni], b0a + kq * KQ_B + ni * 64);
+  AT ax, ay;
+  ws_lds(ax, a0 + kq * KQ_A);
+  // an odd number of steps per k-quad swaps the roles of ax / ay from one k-quad to the next
+  bool more;
+#pragma unroll 1
+  for (;;) {
+    more = kqm != 0;
+    int kqn = more ? __ffs(kqm) - 1 : kq;
+    kqm &= kqm - 1;
+    ws_mma_kquad<C, NF, AT>(acc, ax, ay, b0, b1, a0 + kq * KQ_A, a0 + kqn * KQ_A, b0a + kqn * KQ_B);
+    if (!more) break;
+    kq = kqn;
+    more = kqm != 0;
+    kqn = more ? __ffs(kqm) - 1 : kq;
+    kqm &= kqm - 1;
+    if (NSTEP & 1) ws_mma_kquad<C, NF, AT>(acc, ay, ax, b1, b0, a0 + kq * KQ_A, a0 + kqn * KQ_A, b0a + kqn * KQ_B);
+    else ws_mma_kquad<C, NF, AT>(acc, ax, ay, b1, b0, a0 + kq * KQ_A, a0 + kqn * KQ_A, b0a + kqn * KQ_B);
+    if (!more) break;
+    kq = kqn;
+  }
+}
+
 template <class C, int NF>
 __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) {
   constexpr int ND = C::ND, P = C::P, NS = C::NS, NB = C::NB, SB = C::SB, NCT = C::NCT;
@@ -670,7 +761,10 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
     if (!(flags & 8)) {
       const double *Ast = S.As + stg * C::A_STAGE + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
-      if (!(C2_WS_DIAG & 256)) ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+      if (!(C2_WS_DIAG & 256)) {
+        if (C::NF0 == C::NF1) ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+        else ws_mma_stage_v1<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+      }
 #if C2_WS_DIAG & 16
       dg_mma += clock64() - dg1;
       dg_cnt += (unsigned long long)__popc((unsigned)h.kqmask[wm]) * ND * NF;
