@@ -563,8 +563,8 @@ def run_ours(a):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE whole-grid launch on one GPU from an `ncu --set full` capture (not
 # measured in the run): keyed by (grid, n_gpus, kernel cfg); chi-tile cache spills, not algorithmic bytes
-TRAFFIC = {(400, 1, 6): 1.026e13}
-TRAFFIC_SOURCE = "ncu, profiles/r1_ncu_dram_wfn_ws_kernel_400.txt"
+TRAFFIC = {(400, 1, 6): 1.069e13}
+TRAFFIC_SOURCE = "ncu, profiles/r2_ncu_dram_wfn_ws_kernel_400.txt"
 
 
 if __name__ == "__main__":
