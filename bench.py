@@ -537,7 +537,7 @@ def run_ours(a):
                                                              "best of 3, on this GPU before the timed region"},
                              "traffic": TRAFFIC.get((a.n, world, cfg["cfg"])), "traffic_unit": "bytes/launch",
                              "traffic_source": TRAFFIC_SOURCE if (a.n, world, cfg["cfg"]) in TRAFFIC else None,
-                             "kernel": f"{'wfn_ws_kernel' if cfg['cfg'] == 6 else 'wfn_grid_kernel'} cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, "
+                             "kernel": f"{'wfn_ws_kernel' if cfg['cfg'] in (6, 12, 13, 14) else 'wfn_grid_kernel'} cfg {cfg['cfg']} (FP64 DMMA, {cfg['threads']} threads, "
                                        f"P={cfg['points_per_tile']}, NB={cfg['mo_block']})", "kernel_ms": kms,
                              "algorithmic_flops_per_launch": flops, "mean_n_act": nact / max(mypts, 1),
                              "peak_source": "measured FP64 mma.sync (DMMA) peak, profiles/r1_fp64_peak_microbench.log; "

@@ -235,7 +235,7 @@ int c2gpu_wfn_create(int natom, const double *xyz, int npri, const int *icenter,
   h->natom = natom; h->npri = npri; h->nmo = nmoocc;
   h->cfg = wfn_choose_config(nmoocc, g_force_cfg);
   // the split-producer kernel keeps every chi tile of a sub-tile in its cache: 80 KB per 32 primitives and CTA
-  if (h->cfg == 6 && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 3;
+  if ((h->cfg == 6 || h->cfg == 14) && g_force_cfg < 0 && (double)((npri + 31) / 32) * 40960.0 * 2.0 * 160.0 > 48e9) h->cfg = 3;
   if (h->cfg >= 9 && h->cfg <= 11 && nmoocc > wfn_cfg_info(h->cfg).NB) {   // the warp kernel holds ONE block of MO columns
     delete h;
     return fail(1, "c2gpu_wfn_create: the forced warp-kernel configuration holds fewer MO columns than nmoocc");

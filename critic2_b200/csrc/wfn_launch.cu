@@ -108,6 +108,13 @@ static std::vector<WfnCfgInfo> build_infos() {
     i.smem[0] = WsCfg<1, 8, 32, 3, 8>::SMEM; i.smem[1] = WsCfg<4, 8, 32, 3, 8>::SMEM; i.smem[2] = W::SMEM;
     v.push_back(i);
   }
+  // id 14: id 6 with the consumer loop of the balanced variants and paired chi rows (WsCfg::DENSE = 2) for systems with many MO
+  // blocks per sub-tile
+  {
+    WfnCfgInfo i = v[6];
+    i.name = "WSd";
+    v.push_back(i);
+  }
   return v;
 }
 
@@ -137,7 +144,11 @@ int wfn_choose_config(int nmo, int force) {
   const double tG = bM <= 1 ? 70.1 : (bM == 2 ? 96.5 : 9 + 40.0 * bM);
   if (bM <= 6 && tG < tM && tG < tL && tG < tW) return 13;   // measured up to five blocks; beyond 384 MOs the 112-column kernels
   if (tM <= tL && tM <= tW) return 8;
-  return tL <= tW ? 4 : 6;
+  if (tL <= tW) return 4;
+  // from eleven 112-column blocks on the generators have slack to give and the denser consumer loop pays (WSd, id 14): 14
+  // blocks 89.3 -> 90.6 % of the DMMA peak, the 28 blocks of BASELINE config 5 89.6 -> 90.9 %; with the 7 blocks of config 4
+  // it loses 1.2 % (the consumers then starve the generators)
+  return bL >= 11 ? 14 : 6;
 }
 
 template <class C>
@@ -195,6 +206,11 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
     if (nd == 1) return launch_ws<WsCfg<1, 8, 32, 3, 8>>(p, grid, st);
     if (nd == 4) return launch_ws<WsCfg<4, 8, 32, 3, 8>>(p, grid, st);
     return launch_ws<WsCfg<10, 8, 32, 3, 8>>(p, grid, st);
+  }
+  if (cfg == 14) {
+    if (nd == 1) return launch_ws<WsCfg<1, 14, 32, 3, 4, 2>>(p, grid, st);
+    if (nd == 4) return launch_ws<WsCfg<4, 14, 32, 3, 4, 2>>(p, grid, st);
+    return launch_ws<WsCfg<10, 14, 32, 3, 4, 2>>(p, grid, st);
   }
   if (cfg == 6) {
     if (nd == 1) return launch_ws<WsCfg<1>>(p, grid, st);

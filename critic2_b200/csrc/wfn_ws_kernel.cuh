@@ -36,8 +36,12 @@ namespace c2 {
 // 112-column blocks would pad too much).  Warp columns 0,1 (warpgroup 0) own NF0 fragments each, 2,3 (warpgroup 1) NF1.
 // NPW_ = producer warps: 4 (one streamer + three generators; with 8 consumer warps 384 threads) or 8 (seven generators, 512
 // threads: for one to four MO blocks, where the generators -- not the tensor pipe -- set the pace).
-template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3, int NPW_ = 4>
+template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3, int NPW_ = 4, int DENSE_ = 0>
 struct WsCfg {
+  // DENSE_: the 4 + 3 fragment split with the consumer loop of the balanced variants (ws_mma_stage; 2: and paired chi rows).
+  // Denser consumers leave the generators less of the FP64 unit, which only pays when the generators have slack to give: many
+  // MO blocks per sub-tile (wfn_choose_config)
+  static constexpr bool DENSE = DENSE_ != 0;
   static constexpr int ND = ND_;
   static constexpr int P = 16, WM = 2;          // points per sub-tile (two 8-point MMA row groups)
   static constexpr int NFRAG = NFRAG_, NB = 8 * NFRAG_;    // MO columns per block
@@ -55,7 +59,7 @@ struct WsCfg {
   // the two consumer warps of a sub-partition carry the same number of fragments: with 4 + 3 the lighter warp gets through
   // its stage even faster and the heavier one runs alone for longer (measured: 88.6 -> 87.4 % on the bench slab, while the
   // 64-column variant gains 4 %)
-  static constexpr bool PAIRS = (ND_ % 2 == 0) && (NF0 == NF1);
+  static constexpr bool PAIRS = (ND_ % 2 == 0) && (NF0 == NF1 || DENSE_ == 2);
   static constexpr int SB = NB + 4;             // B row stride in doubles (= 4 mod 16)
   static constexpr int A_STAGE = KC * ND * P, B_STAGE = KC * SB;
   static constexpr int TSLOTS = 8;              // tile-info ring (>= NS + 3, see ws_generator)
@@ -762,7 +766,7 @@ __device__ void ws_consumer(const WfnParams &p, const WsShared<C> &S, int ctid) 
       const double *Ast = S.As + stg * C::A_STAGE + aoff;
       const double *Bst = S.Bs + stg * C::B_STAGE + (lane & 3) * SB + f0 * 8 + (lane >> 2);
       if (!(C2_WS_DIAG & 256)) {
-        if (C::NF0 == C::NF1) ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
+        if (C::NF0 == C::NF1 || C::DENSE) ws_mma_stage<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
         else ws_mma_stage_v1<C, NF>(acc, Ast, Bst, (unsigned)h.kqmask[wm]);
       }
 #if C2_WS_DIAG & 16

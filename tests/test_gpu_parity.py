@@ -72,7 +72,7 @@ def test_cube_cell_grid_ragged(G, O):
     assert (ref["f"] == 0).any()
 
 
-@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12, 13])
+@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12, 13, 14])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_all_configs(G, O, cfg, variant):
     """24-atom def2-TZVP-shaped synthetic molecule through every block-synchronous and warp-specialised configuration
@@ -654,7 +654,7 @@ def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
 
 
 # ---- round 2: the multi-MO-block paths of the tensor-core kernels -------------------------------------------------------
-@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12, 13])
+@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12, 13, 14])
 @pytest.mark.parametrize("nmo", [113, 300])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
@@ -678,7 +678,7 @@ def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
     print(cfg, nmo, variant, c["nblk"], _compare_cube(got, ref))
 
 
-@pytest.mark.parametrize("cfg", [4, 6, 13])
+@pytest.mark.parametrize("cfg", [4, 6, 13, 14])
 def test_nci_and_points_multi_block(G, O, cfg):
     """NCIPLOT evaluation and a ragged point list with three MO blocks (classification identical, nuclei flagged)."""
     from critic2_b200 import drivers, synth
@@ -1001,7 +1001,7 @@ def test_warp_kernel_points_nder_nci_core_gkin_mo(G, O, cfg):
         G.set_option("wfn_cfg", -1)
 
 
-@pytest.mark.parametrize("cfg,nmo", [(9, 8), (11, 20), (8, 40), (4, 120), (6, 120), (13, 150)])
+@pytest.mark.parametrize("cfg,nmo", [(9, 8), (11, 20), (8, 40), (4, 120), (6, 120), (13, 150), (14, 120)])
 def test_g_and_h_functions_through_every_kernel_family(G, O, cfg, nmo):
     """Primitive types 21-56 (g and h shells: l = 4, 5 -- the top of calculate_mo_gto's type table,
     wfn_private@proc.F90:2695-2705; powers up to x^7 in the second derivatives) through the warp, block-synchronous and

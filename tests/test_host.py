@@ -212,7 +212,8 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     assert [pick(n) for n in (25, 48, 64)] == [8, 8, 8]
     # WS64g (64-column blocks, seven generator warps) from 65 MOs on since its generators evaluate shell-wise
     assert [pick(n) for n in (65, 100, 112, 113, 128, 129, 150, 192, 193, 224, 225, 256, 300, 320, 330, 350, 384)] == [13] * 17
-    assert [pick(n) for n in (385, 400, 780, 3120)] == [6, 6, 6, 6]      # incl. BASELINE configs 4 and 5
+    assert [pick(n) for n in (385, 400, 780, 1120)] == [6, 6, 6, 6]      # incl. BASELINE config 4
+    assert [pick(n) for n in (1121, 1560, 3120)] == [14, 14, 14]         # dense consumer loop from eleven blocks; BASELINE config 5
 
 
 def test_aimpac_wfn_round_trip(tmp_path):
