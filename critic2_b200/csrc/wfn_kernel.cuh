@@ -263,17 +263,28 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_grid_kernel(const __grid_c
 #pragma unroll
           for (int d = 0; d < ND; d++) chi[d] = 0.0;
           bool nz = false;
-          if (gk < kact && pvalid) {
-            const int prim = pr_list[gk];
+          const bool real = gk < kact && pvalid;
+          const int prim = real ? pr_list[gk] : 0;
+          const uchar4 l = real ? reinterpret_cast<const uchar4 *>(w.prim_l)[prim] : make_uchar4(0, 0, 0, 0);
+          const bool big = __any_sync(~0u, (l.x | l.y | l.z) > 2);   // f shells and up: powers by multiplication
+          if (real) {
             const int sh = w.prim_shell[prim];
             const double4 xa = w.shell_xa[sh];
             const double2 cut = w.shell_cut[sh];
-            const double dx = px - xa.x, dy = py - xa.y, dz = pz - xa.z;
-            const double d2 = dx * dx + dy * dy + dz * dz;
-            if (within_cut(dx, dy, dz, d2, cut.x, cut.y)) {          // :2747
-              const uchar4 l = reinterpret_cast<const uchar4 *>(w.prim_l)[prim];
-              const double ex = exp(-xa.w * d2);                      // :2749
-              prim_chi_mode<ND>(dx, dy, dz, l.x, l.y, l.z, xa.w, ex, p.chi_mode, chi);
+            ShellAxis ax, ay;
+            ax.x = px - xa.x; ay.x = py - xa.y;
+            const double zr = pz - xa.z;
+            ax.x2 = ax.x * ax.x; ay.x2 = ay.x * ay.x;
+            const double z2 = zr * zr;
+            const double d2 = __dadd_rn(__dadd_rn(ax.x2, ay.x2), z2);
+            if (within_cut(ax.x, ay.x, zr, d2, cut.x, cut.y)) {      // :2747
+              const double ta = xa.w + xa.w;
+              ShellAxisE az;
+              shell_axis_setup(ax, ta);
+              shell_axis_setup(ay, ta);
+              shell_axis_setup(az, zr, z2, ta, exp_neg(-xa.w * d2));  // :2749
+              if (big) shell_prim_chi<ND, true>(ax, ay, az, l.x, l.y, l.z, ta, p.chi_mode, chi);   // :2755-2768
+              else shell_prim_chi<ND, false>(ax, ay, az, l.x, l.y, l.z, ta, p.chi_mode, chi);
               nz = true;
             }
           }

@@ -27,6 +27,13 @@ long g_launches = 0;
   X(7, "S3w", 4, 3, 3, 12, 2) \
   X(8, "M2", 2, 4, 8, 16, 2)
 
+// ids after the warp-specialised variants (12..14): M2 with 32-column blocks for 25..32 MOs (one fragment per warp column;
+// M2 pads them to 64 columns); with two and with three CTAs per SM
+#define C2_WFN_CONFIGS3(X)   \
+  X(15, "M2h", 2, 4, 4, 16, 2) \
+  X(16, "M2h3", 2, 4, 4, 16, 3) \
+  X(17, "M2t", 2, 3, 6, 12, 2)
+
 // warp-autonomous kernel (ids 9, 10, 11): NF fragments of 8 MO columns, CTAs per SM (register budget: 65536 / (128 x CTAS))
 #define C2_WARP_CONFIGS(X) \
   X(1, 4)                  \
@@ -115,6 +122,19 @@ static std::vector<WfnCfgInfo> build_infos() {
     i.name = "WSd";
     v.push_back(i);
   }
+#define X(ID, NAME, WM, WN, NF, KC, CTAS)                                                            \
+  {                                                                                                  \
+    WfnCfgInfo i;                                                                                    \
+    i.name = NAME; i.wm = WM; i.wn = WN; i.ni = NF; i.kc = KC; i.ctas = CTAS;                        \
+    i.P = 8 * WM; i.NB = 8 * NF; i.NT = 32 * WM * WN;                                                \
+    tile_shape(i.P, i.ta, i.tb, i.tc);                                                               \
+    i.smem[0] = TileCfg<1, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[1] = TileCfg<4, WM, WN, NF, KC, CTAS>::SMEM;                                              \
+    i.smem[2] = TileCfg<10, WM, WN, NF, KC, CTAS>::SMEM;                                             \
+    v.push_back(i);                                                                                  \
+  }
+  C2_WFN_CONFIGS3(X)
+#undef X
   return v;
 }
 
@@ -131,6 +151,10 @@ int wfn_choose_config(int nmo, int force) {
   // up to 24 MOs: the warp-autonomous kernel (wfn_warp_kernel.cuh).  Measured on BASELINE config 1 (h2o-aqz 128^3, 5 MOs):
   // 1.17 ms against 1.46 ms for S1; config 2 (benzene-adz NCIPLOT 200^3, 21 MOs): 13.4 ms against 17.3 ms for S3w
   if (nfrag <= 3) return 8 + nfrag;
+  // 25..48 MOs: M2 with 32- / 48-column blocks instead of padding to 64 (60-atom molecule, 160^3: 36.4 ms for 25-32 MOs with
+  // three CTAs per SM and 47.7 ms for 33-48 MOs against 55.7 ms for M2)
+  if (nmo <= 32) return 16;
+  if (nmo <= 48) return 17;
   // Measured cost model (60-atom molecule, 1770 primitives, 160^3; ms; tools/probe_mid.py, profiles/r2_probe_mid.log):
   //   blocks          1      2      3      4      5
   //   M2    (64)     57.2  110.5  163.7  216.9  269.9    53.5 per block + 3.5
@@ -225,6 +249,7 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
   }
   C2_WFN_CONFIGS(X)
   C2_WFN_CONFIGS2(X)
+  C2_WFN_CONFIGS3(X)
 #undef X
   return cudaErrorInvalidValue;
 }

@@ -72,7 +72,7 @@ def test_cube_cell_grid_ragged(G, O):
     assert (ref["f"] == 0).any()
 
 
-@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12, 13, 14])
+@pytest.mark.parametrize("cfg", [0, 1, 2, 3, 4, 5, 6, 7, 8, 12, 13, 14, 15, 16, 17])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_all_configs(G, O, cfg, variant):
     """24-atom def2-TZVP-shaped synthetic molecule through every block-synchronous and warp-specialised configuration
@@ -654,7 +654,7 @@ def test_nci_interleaved_parts_with_the_two_pass_epilogue(G):
 
 
 # ---- round 2: the multi-MO-block paths of the tensor-core kernels -------------------------------------------------------
-@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12, 13, 14])
+@pytest.mark.parametrize("cfg", [3, 4, 6, 8, 12, 13, 14, 16, 17])
 @pytest.mark.parametrize("nmo", [113, 300])
 @pytest.mark.parametrize("variant", ["rhf", "uhf_edf"])
 def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):

@@ -209,7 +209,7 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     pick = lambda n: L.c2gpu_wfn_choose_config(n)
     assert [pick(n) for n in (1, 5, 8)] == [9, 9, 9]
     assert [pick(n) for n in (9, 16, 17, 21, 24)] == [10, 10, 11, 11, 11]
-    assert [pick(n) for n in (25, 48, 64)] == [8, 8, 8]
+    assert [pick(n) for n in (25, 32, 33, 48, 49, 64)] == [16, 16, 17, 17, 8, 8]   # M2 with 32- / 48- / 64-column blocks
     # WS64g (64-column blocks, seven generator warps) from 65 MOs on since its generators evaluate shell-wise
     assert [pick(n) for n in (65, 100, 112, 113, 128, 129, 150, 192, 193, 224, 225, 256, 300, 320, 330, 350, 384)] == [13] * 17
     assert [pick(n) for n in (385, 400, 780, 1120)] == [6, 6, 6, 6]      # incl. BASELINE config 4
