@@ -166,7 +166,9 @@ int wfn_choose_config(int nmo, int force) {
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
   const double tM = 53.5 * bM + 3.5, tL = 96 * bL + 6, tW = 102.3 + 50.1 * bL;
   const double tG = bM <= 1 ? 70.1 : (bM == 2 ? 96.5 : 9 + 40.0 * bM);
-  if (bM <= 6 && tG < tM && tG < tL && tG < tW) return 13;   // measured up to five blocks; beyond 384 MOs the 112-column kernels
+  // the model holds to 1 % up to nine 64-column blocks (7: 288.5 ms measured / 289 model, 9: 368.2 / 369; WS with 4 / 5 blocks:
+  // 301.8 / 352.1), so WS64g also takes 385-512 and 561-576 MOs
+  if (bM <= 9 && tG < tM && tG < tL && tG < tW) return 13;
   if (tM <= tL && tM <= tW) return 8;
   if (tL <= tW) return 4;
   // from eleven 112-column blocks on the generators have slack to give and the denser consumer loop pays (WSd, id 14): 14
