@@ -171,10 +171,10 @@ int wfn_choose_config(int nmo, int force) {
   if (bM <= 9 && tG < tM && tG < tL && tG < tW) return 13;
   if (tM <= tL && tM <= tW) return 8;
   if (tL <= tW) return 4;
-  // from eleven 112-column blocks on the generators have slack to give and the denser consumer loop pays (WSd, id 14): 14
-  // blocks 89.3 -> 90.6 % of the DMMA peak, the 28 blocks of BASELINE config 5 89.6 -> 90.9 %; with the 7 blocks of config 4
-  // it loses 1.2 % (the consumers then starve the generators)
-  return bL >= 11 ? 14 : 6;
+  // from nine 112-column blocks on the generators have slack to give and the denser consumer loop pays (WSd, id 14); bench
+  // molecule, central slab, % of the DMMA peak for 7 / 8 / 9 / 10 / 14 blocks: WS 88.8 / 89.6 / 89.7 / 89.7 / 89.3, WSd 87.6 /
+  // 89.6 / 90.8 / 91.0 / 90.6; the 28 blocks of BASELINE config 5: 89.6 -> 90.9
+  return bL >= 9 ? 14 : 6;
 }
 
 template <class C>

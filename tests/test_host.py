@@ -213,8 +213,8 @@ def test_kernel_configuration_choice_follows_the_measured_cost_model():
     # WS64g (64-column blocks, seven generator warps) from 65 MOs on since its generators evaluate shell-wise
     assert [pick(n) for n in (65, 100, 112, 113, 128, 129, 150, 192, 193, 224, 225, 256, 300, 320, 330, 350, 384)] == [13] * 17
     assert [pick(n) for n in (385, 448, 512, 570)] == [13] * 4          # the cost model holds up to nine 64-column blocks
-    assert [pick(n) for n in (513, 560, 577, 780, 1120)] == [6] * 5      # incl. BASELINE config 4
-    assert [pick(n) for n in (1121, 1560, 3120)] == [14, 14, 14]         # dense consumer loop from eleven blocks; BASELINE config 5
+    assert [pick(n) for n in (513, 560, 577, 780, 896)] == [6] * 5       # incl. BASELINE config 4
+    assert [pick(n) for n in (897, 1120, 1560, 3120)] == [14] * 4        # dense consumer loop from nine blocks; BASELINE config 5
 
 
 def test_aimpac_wfn_round_trip(tmp_path):
