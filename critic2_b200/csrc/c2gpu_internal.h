@@ -19,7 +19,7 @@ struct WfnCfgInfo {
   size_t smem[3];             // dynamic shared memory for ND = 1, 4, 10
 };
 int wfn_num_configs();
-inline bool wfn_is_ws(int cfg) { return cfg == 6 || (cfg >= 12 && cfg <= 14) || (cfg >= 18 && cfg <= 20); }   // warp-specialised kernel and its variants
+inline bool wfn_is_ws(int cfg) { return cfg == 6 || cfg == 12 || cfg == 13 || cfg == 14; }   // warp-specialised kernel and its variants
 const WfnCfgInfo &wfn_cfg_info(int cfg);
 // cfg minimising the padded MO count (then the larger tile); `force` >= 0 overrides
 int wfn_choose_config(int nmo, int force);

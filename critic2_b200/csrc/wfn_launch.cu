@@ -135,10 +135,6 @@ static std::vector<WfnCfgInfo> build_infos() {
   }
   C2_WFN_CONFIGS3(X)
 #undef X
-  // ids 18, 19, 20: ids 6, 14, 13 without a streamer warp of their own (WsCfg::MERGE: generator warp 0 also issues the stages)
-  { WfnCfgInfo i = v[6]; i.name = "WSm"; v.push_back(i); }
-  { WfnCfgInfo i = v[14]; i.name = "WSdm"; v.push_back(i); }
-  { WfnCfgInfo i = v[13]; i.name = "WS64gm"; v.push_back(i); }
   return v;
 }
 
@@ -236,21 +232,6 @@ cudaError_t wfn_launch(int cfg, int nd, const WfnParams &p, int grid, cudaStream
     if (nd == 1) return launch_ws<WsCfg<1, 8, 32, 3, 8>>(p, grid, st);
     if (nd == 4) return launch_ws<WsCfg<4, 8, 32, 3, 8>>(p, grid, st);
     return launch_ws<WsCfg<10, 8, 32, 3, 8>>(p, grid, st);
-  }
-  if (cfg == 18) {
-    if (nd == 1) return launch_ws<WsCfg<1, 14, 32, 3, 4, 0, 1>>(p, grid, st);
-    if (nd == 4) return launch_ws<WsCfg<4, 14, 32, 3, 4, 0, 1>>(p, grid, st);
-    return launch_ws<WsCfg<10, 14, 32, 3, 4, 0, 1>>(p, grid, st);
-  }
-  if (cfg == 19) {
-    if (nd == 1) return launch_ws<WsCfg<1, 14, 32, 3, 4, 2, 1>>(p, grid, st);
-    if (nd == 4) return launch_ws<WsCfg<4, 14, 32, 3, 4, 2, 1>>(p, grid, st);
-    return launch_ws<WsCfg<10, 14, 32, 3, 4, 2, 1>>(p, grid, st);
-  }
-  if (cfg == 20) {
-    if (nd == 1) return launch_ws<WsCfg<1, 8, 32, 3, 8, 0, 1>>(p, grid, st);
-    if (nd == 4) return launch_ws<WsCfg<4, 8, 32, 3, 8, 0, 1>>(p, grid, st);
-    return launch_ws<WsCfg<10, 8, 32, 3, 8, 0, 1>>(p, grid, st);
   }
   if (cfg == 14) {
     if (nd == 1) return launch_ws<WsCfg<1, 14, 32, 3, 4, 2>>(p, grid, st);

@@ -36,12 +36,8 @@ namespace c2 {
 // 112-column blocks would pad too much).  Warp columns 0,1 (warpgroup 0) own NF0 fragments each, 2,3 (warpgroup 1) NF1.
 // NPW_ = producer warps: 4 (one streamer + three generators; with 8 consumer warps 384 threads) or 8 (seven generators, 512
 // threads: for one to four MO blocks, where the generators -- not the tensor pipe -- set the pace).
-template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3, int NPW_ = 4, int DENSE_ = 0, int MERGE_ = 0>
+template <int ND_, int NFRAG_ = 14, int KC_ = 32, int NS_ = 3, int NPW_ = 4, int DENSE_ = 0>
 struct WsCfg {
-  // MERGE_: no streamer warp of its own -- every producer warp generates chi tiles and generator warp 0 also issues the
-  // stages, polling the stage / tile barriers between its shell pairs (ws_stream_poll).  The streamer warp spends its life
-  // waiting; as a generator it adds a third to the generators' capacity (the sub-partition it sits on had none)
-  static constexpr bool MERGE = MERGE_ != 0;
   // DENSE_: the 4 + 3 fragment split with the consumer loop of the balanced variants (ws_mma_stage; 2: and paired chi rows).
   // Denser consumers leave the generators less of the FP64 unit, which only pays when the generators have slack to give: many
   // MO blocks per sub-tile (wfn_choose_config)
@@ -189,111 +185,13 @@ __device__ __forceinline__ void ws_store_chi(double *Aq, int k, int pt, const do
   }
 }
 
-// ---- the streamer's work as a resumable state machine (WsCfg::MERGE) -------------------------------------------------
-struct WsStreamState {
-  unsigned it, tcount, it0;   // stage counter, tile counter, first stage of the current tile
-  int ph;                     // 0 next tile, 1 issue stages, 2 drain, 3 data-less tile, 4 exit stage, 5 done
-  int blk, cc, kact, nch, tslot;
-};
-
-// Makes whatever progress the barriers allow and returns (true once the exit stage has been issued).  Called by all 32
-// lanes of generator warp 0; the state lives in shared memory so that it costs the generator code no registers.
 template <class C>
-__device__ __noinline__ bool ws_stream_poll(const WfnParams *pp, WsShared<C> S, WsStreamState *ss, int lane) {
-  constexpr int KC = C::KC, NS = C::NS, NB = C::NB, SB = C::SB;
-  const WfnParams &p = *pp;
-  const WfnDev &w = p.w;
-  unsigned it = ss->it, tcount = ss->tcount, it0 = ss->it0;
-  int ph = ss->ph, blk = ss->blk, cc = ss->cc, kact = ss->kact, nch = ss->nch, tslot = ss->tslot;
-  __syncwarp();
-  for (;;) {
-    const int buf = tcount & 1;
-    if (ph == 0) {
-      if (!mbar_test(&S.ready[buf], (tcount >> 1) & 1u)) break;
-      fence_proxy_async_global();
-      const WsTileDesc td = S.tdesc[buf];
-      if (td.flags & 1) ph = 4;
-      else { kact = td.kact; nch = td.nch; tslot = td.tslot; blk = 0; cc = 0; it0 = it; ph = kact == 0 ? 3 : 1; }
-    } else if (ph == 1) {
-      const int stg = it % NS;
-      if (!mbar_test(&S.empty[stg], ((it / NS) & 1u) ^ 1u)) break;
-      const int2 *pr_list = reinterpret_cast<const int2 *>(p.scratch + (size_t)blockIdx.x * (p.shell_cap + 4 * p.prim_cap) + p.shell_cap) +
-                            (size_t)buf * p.prim_cap;
-      const double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::ACHUNK;
-      const int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * 8;
-      const int c = (blk & 1) ? nch - 1 - cc : cc;     // zigzag over the chunks (see ws_streamer)
-      const int nrow = min(KC, kact - c * KC);
-      const int prim = lane < nrow ? pr_list[c * KC + lane].x : 0;
-      const int prim2 = (KC > 32 && lane + 32 < nrow) ? pr_list[c * KC + lane + 32].x : 0;
-      const int nz = lane < C::NKQ ? nzbase[c * C::NKQ + lane] : 0;
-      const unsigned m0 = __ballot_sync(~0u, (nz & 1) != 0), m1 = __ballot_sync(~0u, (nz & 2) != 0);
-      if (lane == 0) {
-        WsStageHdr &h = S.hdr[stg];
-        h.kqmask[0] = (int)m0; h.kqmask[1] = (int)m1;
-        h.flags = (cc == 0 ? 1 : 0) | (cc == nch - 1 ? 2 : 0) | ((cc == nch - 1 && blk == p.nblk - 1) ? 4 : 0);
-        h.blk = blk; h.tslot = tslot;
-      }
-      __syncwarp();
-      if (lane == 0) {
-        mbar_expect_tx(&S.full[stg], (uint32_t)(nrow * NB * sizeof(double)) + (uint32_t)(C::A_STAGE * sizeof(double)));
-        tma_bulk_g2s(S.As + stg * C::A_STAGE, agbase + (size_t)c * C::A_STAGE, (uint32_t)(C::A_STAGE * sizeof(double)), &S.full[stg]);
-      }
-      __syncwarp();
-      if (lane < nrow)
-        tma_bulk_g2s(S.Bs + stg * C::B_STAGE + lane * SB, w.cmoT + (size_t)prim * w.ldc + (size_t)blk * NB,
-                     (uint32_t)(NB * sizeof(double)), &S.full[stg]);
-      if (KC > 32 && lane + 32 < nrow)
-        tma_bulk_g2s(S.Bs + stg * C::B_STAGE + (lane + 32) * SB, w.cmoT + (size_t)prim2 * w.ldc + (size_t)blk * NB,
-                     (uint32_t)(NB * sizeof(double)), &S.full[stg]);
-      it++;
-      if (++cc == nch) { cc = 0; if (++blk == p.nblk) ph = 2; }
-    } else if (ph == 3 || ph == 4) {
-      const int stg = it % NS;
-      if (!mbar_test(&S.empty[stg], ((it / NS) & 1u) ^ 1u)) break;
-      if (lane == 0) {
-        WsStageHdr &h = S.hdr[stg];
-        h.flags = ph == 3 ? (1 | 2 | 4 | 8) : 16; h.blk = 0; h.tslot = ph == 3 ? tslot : 0;
-        mbar_expect_tx(&S.full[stg], 0u);
-      }
-      __syncwarp();
-      it++;
-      ph = ph == 3 ? 2 : 5;
-    } else if (ph == 2) {   // every load of the tile has landed -> the cache buffer goes back to the generators
-      const unsigned first = it - it0 > (unsigned)NS ? it - NS : it0;
-      bool all = true;
-      for (unsigned i = first; i < it && all; i++) all = mbar_test(&S.full[i % NS], (i / NS) & 1u);
-      if (!all) break;
-      if (lane == 0) mbar_arrive(&S.freeb[buf]);
-      __syncwarp();
-      tcount++;
-      ph = 0;
-    } else
-      break;
-  }
-  if (lane == 0) {
-    ss->it = it; ss->tcount = tcount; ss->it0 = it0; ss->ph = ph; ss->blk = blk; ss->cc = cc; ss->kact = kact; ss->nch = nch;
-    ss->tslot = tslot;
-  }
-  __syncwarp();
-  return ph == 5;
-}
-
-template <class C>
-__device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid, WsStreamState *ss) {
-  constexpr int ND = C::ND, P = C::P, KC = C::KC, NGW = C::MERGE ? C::NPW : C::NPW - 1, NGT = 32 * NGW;
+__device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid) {
+  constexpr int ND = C::ND, P = C::P, KC = C::KC, NGW = C::NPW - 1, NGT = 32 * NGW;
   const int lane = gtid & 31, warp = gtid >> 5;
   const int pt = gtid & 15;
   const WfnDev &w = p.w;
   const GridDesc &g = p.g;
-  // WsCfg::MERGE: generator warp 0 is also the streamer; it lets the stage pipeline advance wherever it would otherwise
-  // only compute or wait
-  auto poll = [&]() -> bool { return (C::MERGE && warp == 0) ? ws_stream_poll<C>(&p, S, ss, lane) : false; };
-  auto wait_free = [&](uint64_t *bar, uint32_t parity) {
-    if (C::MERGE && warp == 0) {
-      while (!mbar_test(bar, parity)) poll();
-    } else
-      mbar_wait(bar, parity);
-  };
   // per-CTA scratch: shell list [shell_cap] then two (primitive, shell) lists [prim_cap] (one per cache buffer)
   int *sh_list = p.scratch + (size_t)blockIdx.x * (p.shell_cap + 4 * p.prim_cap);
   int2 *pr_list0 = reinterpret_cast<int2 *>(sh_list + p.shell_cap);
@@ -336,7 +234,6 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid,
     named_bar_sync(2, NGT);
     int ns = 0;
     for (int base = 0; base < w.nshell; base += NGT) {
-      poll();
       int s = base + gtid;
       bool act = false;
       if (s < w.nshell) {
@@ -401,7 +298,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid,
 #if C2_WS_DIAG & 16
       gg_t0 = clock64();
 #endif
-      wait_free(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
+      mbar_wait(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
 #if C2_WS_DIAG & 16
       gg_t1 = clock64(); gg_free += gg_t1 - gg_t0;
 #endif
@@ -411,7 +308,6 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid,
       // evaluation below depends on ONE global load per shell ------------------------------------------------------------
       int kact = 0, nact_sh = 0;
       for (int base = 0; base < ns; base += NGT) {
-        poll();
         int j = base + gtid, cnt = 0, pb = 0, s = 0;
         if (j < ns) {
           s = sh_list[j];
@@ -477,7 +373,6 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid,
 #pragma unroll
       for (int d = 0; d < ND; d++) zero[d] = 0.0;
       for (int j = warp; 2 * j < nact_sh; j += NGW) {
-        poll();
         const int si = 2 * j + (hsh >> 4);
         const bool has = si < nact_sh;
         double4 xa = make_double4(0.0, 0.0, 0.0, 0.0), r1 = make_double4(0.0, 0.0, 0.0, 0.0), r2 = r1;
@@ -567,19 +462,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid,
     if (warp == 1) { o[4] = gg_free; o[5] = gg_s2; o[6] = gg_chi; o[7] = clock64() - gg_start; }
   }
 #endif
-  if (C::MERGE) {
-    if (warp == 0) {   // exit descriptor, then keep streaming until the exit stage is out
-      const int buf = tcount & 1;
-      wait_free(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
-      if (lane == 0) {
-        WsTileDesc &td = S.tdesc[buf];
-        td.kact = 0; td.nch = 0; td.tslot = 0; td.flags = 1;
-        mbar_arrive(&S.ready[buf]);
-      }
-      __syncwarp();
-      while (!poll()) {}
-    }
-  } else if (gtid == 0) {   // exit descriptor
+  if (gtid == 0) {   // exit descriptor
     const int buf = tcount & 1;
     mbar_wait(&S.freeb[buf], ((tcount >> 1) & 1u) ^ 1u);
     WsTileDesc &td = S.tdesc[buf];
@@ -1036,7 +919,6 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   __shared__ WsTileDesc s_tdesc[2];
   __shared__ double s_pred[C::NPW * 6], s_pbb[12];
   __shared__ int s_pcnt[C::NPW], s_pint[4];
-  __shared__ WsStreamState s_stream;
   WsShared<C> S;
   S.As = reinterpret_cast<double *>(smem_raw);
   S.Bs = S.As + C::NS * C::A_STAGE;
@@ -1051,8 +933,6 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   const int tid = threadIdx.x;
 #endif
   if (tid == 0) {
-    s_stream.it = 0; s_stream.tcount = 0; s_stream.it0 = 0; s_stream.ph = 0; s_stream.blk = 0; s_stream.cc = 0;
-    s_stream.kact = 0; s_stream.nch = 0; s_stream.tslot = 0;
     for (int s = 0; s < C::NS; s++) {
       mbar_init(&s_full[s], 1);            // the streamer's arrive.expect_tx (+ the TMA byte count)
       mbar_init(&s_empty[s], C::NCW);      // one arrival per consumer warp
@@ -1067,9 +947,8 @@ __global__ void __launch_bounds__(C::NT, 1) wfn_ws_kernel(const __grid_constant_
   constexpr bool REBALANCE = C::REG_CONS4 != C::REG_LAUNCH || C::REG_PROD != C::REG_LAUNCH;
   if (tid >= C::NCT) {
     if (REBALANCE) { if (C::REG_PROD <= C::REG_LAUNCH) reg_dec<C::REG_PROD>(); else reg_inc<C::REG_PROD>(); }
-    if (C::MERGE) ws_generator<C>(p, S, tid - C::NCT, &s_stream);
-    else if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
-    else ws_generator<C>(p, S, tid - C::NCT - 32, &s_stream);
+    if (tid < C::NCT + 32) ws_streamer<C>(p, S, tid - C::NCT);
+    else ws_generator<C>(p, S, tid - C::NCT - 32);
   } else if (tid < 128) {
     if (REBALANCE) reg_inc<C::REG_CONS4>();
     ws_consumer<C, C::NF0>(p, S, tid);

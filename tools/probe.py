@@ -49,7 +49,7 @@ for cfg in [int(c) for c in a.cfgs.split(",")]:
               f"{ms:.1f} ms -> {npts / ms * 1e3:.3e} pts/s, {flops / ms / 1e9:.2f} TFLOP/s algorithmic "
               f"({flops / ms / 1e9 / 37.1 * 100:.1f}% of 37.1)", flush=True)
     L = gpu.lib()
-    if hasattr(L, "c2gpu_ws_diag_read") and cfg in (6, 12, 13):   # diagnostic build (tools/ws_diag.sh, bit 16)
+    if hasattr(L, "c2gpu_ws_diag_read") and cfg in (6, 12, 13, 14, 18, 19, 20):   # diagnostic build (tools/ws_diag.sh, bit 16)
         import ctypes as C
         nsm = torch.cuda.get_device_properties(0).multi_processor_count
         buf = (C.c_ulonglong * (nsm * 64))()
@@ -67,7 +67,7 @@ for cfg in [int(c) for c in a.cfgs.split(",")]:
         tot = 16 * (d[:, :4, 2] + d[:, 4:, 2]) / np.maximum(d[:, :4, 3], d[:, 4:, 3])
         print(f"  DMMA pipe cycles per sub-partition / alive cycles: {100 * tot.mean():.1f} % (by sub-partition "
               f"{[round(100 * tot[:, j].mean(), 1) for j in range(4)]})")
-    if hasattr(L, "c2gpu_ws_gdiag_read") and cfg in (6, 12, 13):
+    if hasattr(L, "c2gpu_ws_gdiag_read") and cfg in (6, 12, 13, 14, 18, 19, 20):
         gb = (C.c_ulonglong * (nsm * 8))()
         L.c2gpu_ws_gdiag_read(gb, nsm * 8)
         gd = np.frombuffer(gb, dtype=np.uint64).reshape(nsm, 2, 4).astype(np.float64)
