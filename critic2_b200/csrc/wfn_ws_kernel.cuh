@@ -649,7 +649,7 @@ __device__ __forceinline__ void ws_lds(double2 &v, uint32_t addr) {
 template <class C, int NF, class AT>
 __device__ __forceinline__ void ws_mma_kquad(double (&acc)[C::ND][NF][2], AT &a_cur, AT &a_oth, const double (&b)[NF], double (&bn)[NF],
                                              uint32_t ak, uint32_t an_first, uint32_t bn_addr) {
-  constexpr int ND = C::ND, SB = C::SB;
+  constexpr int ND = C::ND;
   constexpr bool PAIRS = C::PAIRS;
   constexpr int NSTEP = PAIRS ? ND / 2 : ND;
   constexpr uint32_t STEP_BYTES = (PAIRS ? 128 : 64) * 8;   // one derivative row = 64 doubles, a pair = 128
