@@ -35,10 +35,13 @@ long g_launches = 0;
   X(17, "M2t", 2, 3, 6, 12, 2)
 
 // warp-autonomous kernel (ids 9, 10, 11): NF fragments of 8 MO columns, CTAs per SM (register budget: 65536 / (128 x CTAS))
+// Since the shell-wise chi code (fewer live registers) one more CTA per SM pays for two and three fragments in spite of ~140
+// bytes of spills: 3 fragments (benzene NCIPLOT 200^3) 13.59 -> 12.59 ms with three CTAs at 168 registers, 2 fragments 20.56 ->
+// 19.69 ms with four at 128; one fragment stays at four (five: 1.19 -> 1.32 ms on h2o 128^3)
 #define C2_WARP_CONFIGS(X) \
   X(1, 4)                  \
-  X(2, 3)                  \
-  X(3, 2)
+  X(2, 4)                  \
+  X(3, 3)
 
 static void tile_shape(int P, int &ta, int &tb, int &tc) {
   switch (P) {
