@@ -179,7 +179,8 @@ __global__ void __launch_bounds__(C::NT, C::CTAS) wfn_warp_kernel(const __grid_c
         // k-quads [0, nq): chi in the A-fragment layout straight from the FP64 pipe, C rows from L1, DMMA.  (A software-
         // pipelined, branch-free version of this loop -- chi of quad q+1 scheduled between the DMMAs of quad q, a
         // branch-free exp -- measured the same: 13.6 against 13.4 ms on benzene 200^3; so did skipping fully masked quads
-        // after the evaluation (14.3 ms) and three CTAs per SM at 168 registers (14.7 ms, spills).  See DESIGN.md.)
+        // after the evaluation (14.3 ms).  Three CTAs per SM at 168 registers: 14.7 ms with that chi code, 12.6 ms with the
+        // shell-wise one, which is what ships.  See DESIGN.md.)
 #pragma unroll 1
         for (int q = 0; q < nq; q++) {
           const int2 e = wl[4 * q + kk];
