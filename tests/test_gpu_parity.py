@@ -1063,3 +1063,45 @@ def test_spin_and_valence_channels_of_rho2(G, O, uhf, cfg, nmo):
         assert fld.channel() is fld and fld.channel(spin=1) is fld.channel(spin=1)
     finally:
         G.set_option("wfn_cfg", -1)
+
+
+@pytest.mark.parametrize("cfg", [-1, 6, 8, 13])
+def test_exp_neg_over_its_whole_range(G, cfg):
+    """The device's own exp for t <= 0 (exp_neg, csrc/wfn_device.cuh: table + degree-6 polynomial; library exp below -700)
+    through the kernels that use it: one s primitive with its cutoff radius pushed out until exp(-a r^2) underflows, so the
+    arguments run from 0 to -1168.  rho = 2 exp(-2 a r^2) against numpy; the argument a r^2 itself carries the rounding of the
+    coordinates (cell frame, ~80 bohr), an error that grows with |t|, hence the |t|-proportional bound.  (With the reference's cutoffs |t| stays below 46.)"""
+    from critic2_b200 import wfn
+    a = 0.73
+    f = wfn.Molwfn(natom=1, xyz=np.zeros((1, 3)), z=np.array([2], np.int32), icenter=np.array([1], np.int32),
+                   itype=np.array([1], np.int32), e=np.array([a]), occ=np.array([2.0]), cmo=np.array([[1.0]]), nmoocc=1)
+    wfn.complete_struct(f)
+    f.dran = np.array([40.0])                      # a r^2 up to 1168: past the underflow of exp
+    f.spcutoff = np.array([40.0])
+    st = cases.mol_structure(f, border=45.0)          # every point inside the molecular cell
+    r = np.concatenate([np.linspace(0.0, 32.0, 4001), np.sqrt(np.array([690.0, 699.9, 700.1, 708.0, 744.0, 760.0]) / a)])
+    u = np.array([0.36, 0.48, 0.8])                # |u| = 1
+    pts = st.r[0][None, :] + r[:, None] * u[None, :]
+    G.set_option("wfn_cfg", cfg)
+    try:
+        fld = G.WfnField(f, st)
+    finally:
+        G.set_option("wfn_cfg", -1)
+    got = fld.points(pts, nder=2, periodic=False)
+    d2 = ((pts - st.r[0]) ** 2).sum(1)
+    chi = np.exp(-a * d2)
+    ref = 2.0 * chi * chi
+    big = ref > 1e-290
+    assert big.sum() > 2500 and (~big).sum() > 50      # rho = 2 chi^2 is checked down to chi = 1e-145 (t = -334); beyond: no NaN,
+                                                       # clean underflow (t down to -1168 runs the library fallback)
+    rel = np.abs(got[big, 0] - ref[big]) / ref[big]
+    # the displacement carries the rounding of the cell-frame coordinates (~80 bohr: ~3e-14 bohr), which enters t = 2 a r^2 as
+    # 4 a r x 3e-14: the bound follows it, so what is tested is that exp_neg adds nothing visible on top
+    bound = 3e-14 + 4.0 * a * r[big] * 3e-14
+    assert np.all(rel < bound), (cfg, float((rel / bound).max()), float(r[big][(rel / bound).argmax()]))
+    assert np.all(got[~big, 0] <= 1e-289) and np.all(np.isfinite(got))
+    # gradient of the same function: -4 a r rho along u
+    gref = (-4.0 * a * ref)[:, None] * (pts - st.r[0])
+    m = big & (r > 0.5)
+    gb = 2.0 * (3e-14 + 4.0 * a * r[m] * 3e-14) + 3e-14 / r[m]      # + the displacement's own relative rounding
+    assert np.all(np.abs(got[m, 1:4] - gref[m]).max(1) / np.abs(gref[m]).max(1) < gb)
