@@ -16,11 +16,14 @@ ap.add_argument("--z0", type=int, default=192)
 ap.add_argument("--z1", type=int, default=208)
 ap.add_argument("--cfgs", type=str, default="3,4")
 ap.add_argument("--small", action="store_true")
+ap.add_argument("--super", type=int, default=0, help="super-tile edge (option 'super'; development A/B)")
 ap.add_argument("--cfg5", action="store_true", help="the 2000-atom molecule of BASELINE config 5")
 ap.add_argument("--nmo", type=int, default=0, help="MO count of the config-4 molecule (default 780)")
 a = ap.parse_args()
 
 gpu.init_devices([0])
+if a.super:
+    gpu.set_option("super", a.super)
 f = synth.config5() if a.cfg5 else synth.small_synthetic() if a.small else (synth.synthetic_molecule(nmo=a.nmo) if a.nmo else synth.config4())
 st = structure.molecular_cell(f.xyz, f.z)
 lo, hi = st.r.min(0) - 6.0, st.r.max(0) + 6.0
