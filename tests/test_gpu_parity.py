@@ -578,7 +578,8 @@ def test_promolecular_many_species_and_table_edges(G, O):
     check_vec(res[:, 4:13], rres[:, 4:13], "hess", rho=rres[:, 0])
 
 
-@pytest.mark.parametrize("name,cfg", [("benzene-adz", -1), ("hooh-atz", -1), ("synth", 3), ("synth", 6)])
+@pytest.mark.parametrize("name,cfg", [("benzene-adz", -1), ("hooh-atz", -1), ("synth", 3), ("synth", 6), ("synth", 13), ("synth", 14),
+                                      ("synth", 16), ("synth", 17)])
 def test_gkin_and_mo_values_on_point_lists(G, O, name, cfg):
     """mesh%fill's remaining properties (meshmod@proc.f90:456-464): res%gkin (three derivative-selected value passes of the
     wavefunction kernels) and MO values (grd nder=-1 -> calculate_mo, a linear pass over a one-MO handle)."""
