@@ -679,7 +679,7 @@ def test_cube_synthetic_multi_block(G, O, cfg, nmo, variant):
     print(cfg, nmo, variant, c["nblk"], _compare_cube(got, ref))
 
 
-@pytest.mark.parametrize("cfg", [4, 6, 13, 14])
+@pytest.mark.parametrize("cfg", [4, 6, 13, 14, 16, 17])
 def test_nci_and_points_multi_block(G, O, cfg):
     """NCIPLOT evaluation and a ragged point list with three MO blocks (classification identical, nuclei flagged)."""
     from critic2_b200 import drivers, synth
@@ -690,7 +690,8 @@ def test_nci_and_points_multi_block(G, O, cfg):
         fld = G.WfnField(f, st)
     finally:
         G.set_option("wfn_cfg", -1)
-    assert fld.config()["nblk"] == (4 if cfg == 13 else 3)
+    c = fld.config()
+    assert c["cfg"] == cfg and c["nblk"] == -(-230 // c["mo_block"]) and c["nblk"] >= 3
     of = _ofield(O, f, st)
     x0, xmat, ns = drivers.nci_grid(st, nstep=(15, 13, 17))
     rrho, rgrad, _ = of.nci(x0, xmat, ns)
