@@ -3,13 +3,17 @@
 // Same mathematics and data layout as wfn_kernel.cuh (see there for the reference citations), different execution
 // model.  ncu on the first version showed the FP64 tensor pipe (DMMA) idle ~38 % of the time because every warp
 // alternated between latency-bound primitive evaluation and MMAs behind one block-wide barrier per chunk.  Here
-//   * 4 PRODUCER warps (one per SM sub-partition) own everything that is not an MMA: super-tile claiming, shell
-//     screening (S1/S2), the chi tiles (A operand) and the bulk-TMA gather of C rows (B operand);
+//   * 4 PRODUCER warps (one per SM sub-partition) own everything that is not an MMA: one STREAMER (bulk-TMA copies of the
+//     chi tiles and of the C rows into the stages) and three GENERATORS (super-tile claiming, shell screening S1/S2, the chi
+//     tiles, evaluated shell by shell one sub-tile ahead into a per-CTA cache in L2);
 //   * 8 CONSUMER warps (two per sub-partition, 4+3 MMA fragments each so that every sub-partition carries 7 of the
 //     14 fragments of a 112-column MO block) only wait on mbarriers, issue DMMAs and run the fused epilogue;
-//   * registers are re-balanced with setmaxnreg (consumers 208, producers 88): the consumers hold 10x4x2 accumulators;
+//   * registers are re-balanced with setmaxnreg (consumers 232 / 184, producers 88): the consumers hold 10x4x2 accumulators;
 //   * stages hand over through full/empty mbarriers (no block-wide barrier in steady state), and the stream of
 //     (sub-tile, MO block, chunk) steps is continuous, so producers run ahead across block and tile boundaries.
+// Variants (WsCfg): 64-column blocks with seven generator warps for a few MO blocks (WS64g), the dense consumer loop with
+// paired chi rows for many MO blocks (WSd), 96-column blocks (WS96, kept for measurements).  What limits the kernel is the
+// FP64 unit's arbitration between the consumers' DMMAs and the generators' ordinary FP64 work: DESIGN.md section 4.
 #pragma once
 #include "wfn_kernel.cuh"
 #include <type_traits>
@@ -17,8 +21,8 @@
 // Development diagnostics (tools/ws_diag.sh builds separate libraries with -DC2_WS_DIAG=bits; the shipped library has 0 and
 // none of this code).  Results of a diagnostic build are NOT valid field values: the bits remove work to see what the
 // tensor pipe is waiting for.  1: the streamer issues no TMA copies (stages complete at once; consumers multiply stale
-// shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: (retired).  16: consumer warps accumulate clock64() spent
-// waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
+// shared memory).  2: the generators skip the chi arithmetic (zeros stored, masks kept).  4: (retired).  16: consumer warps accumulate
+// clock64() spent waiting for a full stage / inside the MMA loop and the DMMA count into g_ws_diag (c2gpu_ws_diag_read).  32: the generators
 // do not store the chi tiles.  64: no exp in the generators.  128: the generators
 // skip the arithmetic of every fourth shell pair (what a fourth generator warp would buy).  256: the consumers issue no
 // DMMAs (the kernel time is then what the producers need when they have the FP64 unit to themselves).
