@@ -163,12 +163,12 @@ int wfn_choose_config(int nmo, int force) {
   //   M2    (64)     57.2  110.5  163.7  216.9  269.9    53.5 per block + 3.5
   //   L1    (112)   102.6  198.6  294.3                  96 per block + 6
   //   WS    (112)   152.3  202.3  252.6                  102.3 + 50.1 per block (generators ahead, chi tiles re-used from L2)
-  //   WS64g (64)     70.1   96.5  129.1  168.9  208.9    generator-bound for one block, then 9 + 40 per block
-  // (first version of WS64g: 92.6 / 119.5 / 157.4 / 198.2 / 239.7.)  WS64g wins from 65 to 384 MOs: 128 MOs 70.8 % of the
-  // DMMA peak, 192: 78.6 %, 256: 79.7 %, 300: 75.4 %; 500-atom config 4 (780 MOs): WS 89.8 % of the peak, L 62 %.
+  //   WS64g (64)     66.5   92.1  128.9  168.8  208.6    generator-bound for one block, then 9 + 40 per block
+  // (first version of WS64g: 92.6 / 119.5 / 157.4 / 198.2 / 239.7.)  WS64g wins from 65 to 384 MOs: 128 MOs 74.2 % of the
+  // DMMA peak, 192: 78.7 %, 256: 79.7 %, 300: 75.5 %; 500-atom config 4 (780 MOs): WS 89.8 % of the peak, L 62 %.
   const int bM = (nmo + 63) / 64, bL = (nmo + 111) / 112;
   const double tM = 53.5 * bM + 3.5, tL = 96 * bL + 6, tW = 102.3 + 50.1 * bL;
-  const double tG = bM <= 1 ? 70.1 : (bM == 2 ? 96.5 : 9 + 40.0 * bM);
+  const double tG = bM <= 1 ? 66.5 : (bM == 2 ? 92.1 : 9 + 40.0 * bM);
   // the model holds to 1 % up to nine 64-column blocks (7: 288.5 ms measured / 289 model, 9: 368.2 / 369; WS with 4 / 5 blocks:
   // 301.8 / 352.1), so WS64g also takes 385-512 and 561-576 MOs
   if (bM <= 9 && tG < tM && tG < tL && tG < tW) return 13;

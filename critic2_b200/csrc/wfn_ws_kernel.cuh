@@ -362,6 +362,7 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       double *agbase = p.acache + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * C::ACHUNK;
       int *nzbase = p.acache_nz + ((size_t)blockIdx.x * 2 + buf) * (size_t)p.acache_chunks * 8;
       for (int q = gtid; q < nquad; q += NGT) nzbase[q] = 0;   // k-quad masks: OR-ed together below
+      if (gtid == 0) S.p_int[2] = 0;                            // next shell pair to evaluate (claimed dynamically)
       __threadfence_block();
       named_bar_sync(2, NGT);   // records and cleared masks visible to every generator thread
       const double px = tp[pt], py = tp[P + pt], pz = tp[2 * P + pt];
@@ -376,7 +377,11 @@ __device__ void ws_generator(const WfnParams &p, const WsShared<C> &S, int gtid)
       double zero[ND];
 #pragma unroll
       for (int d = 0; d < ND; d++) zero[d] = 0.0;
-      for (int j = warp; 2 * j < nact_sh; j += NGW) {
+      for (;;) {   // shell pairs are claimed one at a time: shells differ in cost by the number of their primitives
+        int j = 0;
+        if (lane == 0) j = atomicAdd(&S.p_int[2], 1);
+        j = __shfl_sync(~0u, j, 0);
+        if (2 * j >= nact_sh) break;
         const int si = 2 * j + (hsh >> 4);
         const bool has = si < nact_sh;
         double4 xa = make_double4(0.0, 0.0, 0.0, 0.0), r1 = make_double4(0.0, 0.0, 0.0, 0.0), r2 = r1;
